@@ -1,0 +1,195 @@
+/*
+ * pte.h -- C ABI of the B200 bulk pod phase-transition engine (libpte.so).
+ *
+ * The reference (highreso-gpu/k8s-watcher) is pure Python and has no FFI or
+ * plugin interface; its per-event path is PodWatcher.handle_pod_event
+ * (watcher/pod_watcher.py:214-241).  This header is the boundary a maintainer
+ * would bind with ctypes to run that path in bulk on a GPU.  Each entry point
+ * cites the reference code it stands in for.
+ *
+ * Conventions: every call returns 0 (PTE_OK) or a negative pte_status; the
+ * text for the last failure on a handle is pte_last_error(h) (h == NULL: the
+ * last failure of a call that had no handle, per thread).  No exceptions cross
+ * the boundary.  The caller owns all host buffers; the engine owns all device
+ * memory for the lifetime of the handle.  A handle is bound to one device and
+ * is not thread-safe: one host thread per handle.  There is NO CPU fallback:
+ * without a CUDA device pte_create fails with PTE_ERR_NO_DEVICE.
+ *
+ * Replay-log record (one pod-watch event; the fields handle_pod_event reads,
+ * pod_watcher.py:162-167,216-217, plus resourceVersion as the order key):
+ *   uid_hi,uid_lo  u64,u64  metadata.uid as a 128-bit integer (never 0:0)
+ *   rv             u64      metadata.resourceVersion; replay order is ascending rv
+ *   ns_id          u32      metadata.namespace, interned by the host log
+ *   phase          u8       PTE_PH_* code (0..62)
+ *   type           u8       PTE_T_ADDED / MODIFIED / DELETED (event['type'], :267)
+ */
+#ifndef PTE_H
+#define PTE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pte_engine* pte_handle;
+
+enum pte_status {
+    PTE_OK = 0,
+    PTE_ERR_INVALID = -1,     /* bad argument */
+    PTE_ERR_CUDA = -2,        /* CUDA runtime error (text in pte_last_error) */
+    PTE_ERR_NO_DEVICE = -3,   /* no usable CUDA device: the engine has no CPU path */
+    PTE_ERR_CAPACITY = -4,    /* more events than max_events / record layout does not fit 64 bits */
+    PTE_ERR_TABLE_FULL = -5,  /* more distinct uids than max_pods */
+    PTE_ERR_BAD_EVENT = -6,   /* type not in {0,1,2}, phase > 62 or uid == 0:0 (the reference would crash
+                                 on such an object at pod_watcher.py:216) */
+    PTE_ERR_UNORDERED = -7,   /* rv not non-decreasing in arrival order and rv span too wide to pre-sort */
+    PTE_ERR_STATE = -8,       /* call out of sequence (e.g. fetch before run) */
+    PTE_ERR_NCCL = -9
+};
+
+enum { PTE_T_ADDED = 0, PTE_T_MODIFIED = 1, PTE_T_DELETED = 2 };
+enum {
+    PTE_PH_PENDING = 0, PTE_PH_RUNNING = 1, PTE_PH_SUCCEEDED = 2, PTE_PH_FAILED = 3, PTE_PH_UNKNOWN = 4,
+    PTE_PH_NULL = 5,      /* status present, status.phase is None */
+    PTE_PH_NOSTATUS = 6,  /* pod.status is None: payload phase "Unknown" (pod_watcher.py:167) */
+    PTE_PH_FIRST_DYNAMIC = 7, PTE_PH_MAX = 62
+};
+
+typedef struct pte_stats {
+    uint64_t n_in;          /* events in the log */
+    uint64_t n_survived;    /* passed should_process_event (:204-212) and the namespace list (:226-229) */
+    uint64_t n_emitted;     /* notifications (R-trace if dedupe == 0, T-trace otherwise) */
+    uint64_t n_tombstones;  /* emitted DELETED events */
+    uint64_t n_pods;        /* distinct uids interned so far on this handle */
+    uint32_t ordered;       /* 1: rv was non-decreasing in arrival order */
+    uint32_t n_launches;    /* kernels launched by this pte_run */
+    float ms_total;         /* device time of this pte_run, CUDA events on the engine stream */
+    float ms_intern;        /* filter + uid interning + record packing */
+    float ms_sort_key;      /* LSD radix passes on the interned key */
+    float ms_diff;          /* segmented adjacent-diff + compaction */
+    float ms_sort_order;    /* LSD radix passes restoring replay order */
+    float ms_assemble;      /* payload column assembly */
+    float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
+    uint32_t n_passes;      /* radix scatter passes run */
+    uint32_t reserved;
+} pte_stats;
+
+/* Parameters of the synthetic replay log (see "Synthetic replay logs" below). */
+typedef struct pte_gen_params {
+    uint64_t seed;
+    uint64_t n_events;       /* events generated for this shard */
+    uint64_t n_pods;         /* pods of this shard (pod index q in [0, n_pods)) */
+    uint32_t dist;           /* 0 uniform pod activity, 1 octave-Zipf (P(rank r) ~ 1/(r+1)) */
+    uint32_t p_del_q24;      /* delete-draw probability * 2^24 */
+    uint32_t p_nostatus_q24; /* P(status is None) * 2^24 */
+    uint32_t p_null_q24;     /* P(status.phase is None) * 2^24 */
+    uint32_t shard;          /* this shard, in [0, n_shards) */
+    uint32_t n_shards;       /* uid-hash shards (one per GPU) */
+} pte_gen_params;
+
+/* ---- lifetime ---------------------------------------------------------- */
+
+/* Number of CUDA devices (0 if none / no driver). */
+int pte_device_count(void);
+
+/* Engine for up to max_events events per log and max_pods distinct uids, on `device`.
+ * Stands in for PodWatcher.__init__ (pod_watcher.py:11-17) as far as the path needs state. */
+int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* out);
+void pte_destroy(pte_handle h);
+const char* pte_last_error(pte_handle h);
+
+/* ---- filters ------------------------------------------------------------ */
+
+/* The two per-event predicates of the reference, as data:
+ *   production_critical_only = (environment == 'production' && watcher.alerts.critical_events_only)
+ *                              -> should_process_event, pod_watcher.py:204-212
+ *   ns_allow[0..n_allow)     = ids of watcher.namespaces; n_allow == 0 means "all namespaces"
+ *                              -> pod_watcher.py:226-229
+ *   ns_filter_on             = 1 if the reference's list was non-empty even though none of its
+ *                              names occurs in the log (then every event is dropped, as upstream). */
+int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_filter_on,
+                    int production_critical_only);
+
+/* ---- input -------------------------------------------------------------- */
+
+/* Copy a log of n events from host columns to the device (replaces the current log).
+ * Stands in for the `for event in stream` producer, pod_watcher.py:264-268. */
+int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
+               const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n);
+
+/* Generate the synthetic log directly in device memory (no reference counterpart). */
+int pte_generate(pte_handle h, const pte_gen_params* p);
+
+/* The same generator on the host, strictly sequential, into caller buffers (no device needed). */
+int pte_generate_host(const pte_gen_params* p, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv,
+                      uint32_t* ns_id, uint8_t* phase, uint8_t* type);
+
+/* Copy the device-resident log back (any pointer may be NULL); cap = capacity of each buffer. */
+int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv, uint32_t* ns_id,
+                 uint8_t* phase, uint8_t* type, uint64_t cap, uint64_t* n_out);
+
+/* ---- the hot path --------------------------------------------------------- */
+
+/* Replay the device-resident log: filters -> uid interning -> LSD radix sort on (key, rv) ->
+ * segmented adjacent-diff + compaction -> restore replay order -> payload columns.
+ * dedupe == 0: every event that would reach the POST site (pod_watcher.py:232-236), the R-trace.
+ * dedupe != 0: only phase transitions and DELETED tombstones (the last-known-phase layer the
+ *              reference's README describes but pod_watcher.py does not implement), the T-trace.
+ * The interning dictionary is cleared at the start of every call. */
+int pte_run(pte_handle h, int dedupe, pte_stats* out);
+
+/* Emitted records of the last pte_run, in replay order, into caller columns (any may be NULL):
+ * idx = arrival index in the ingested log, key = interned 64-bit uid key.
+ * Stands in for the payload hand-off at pod_watcher.py:232-236. */
+int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t* ns_id,
+              uint8_t* phase, uint8_t* type, uint64_t cap, uint64_t* n_out);
+
+/* Order-sensitive 64-bit digest of the emitted records (position, rv, uid, ns, phase, type);
+ * same arithmetic as oracle/oracle.c rec_digest.  For parity at sizes too big to compare in full. */
+int pte_digest(pte_handle h, uint64_t* out);
+
+/* ---- host helpers ------------------------------------------------------- */
+
+/* Pinned host memory for ingest / fetch buffers (plain malloc'd buffers work too, slower). */
+void* pte_host_alloc(size_t bytes);
+void pte_host_free(void* p);
+
+/* Shard of a uid when a log is split across n_shards engines (one per GPU). */
+uint32_t pte_shard_of(uint64_t uid_hi, uint64_t uid_lo, uint32_t n_shards);
+
+/* Stable LSD radix sort of n u64 records on bits [bit_lo, bit_hi), through the device sort
+ * kernels, in place in the caller's host array.  Test hook for the sort in isolation. */
+int pte_debug_sort_u64(pte_handle h, uint64_t* records, uint64_t n, int bit_lo, int bit_hi);
+
+/* ---- multi-GPU: one engine per process/GPU, a single collective --------- */
+
+/* NCCL bootstrap: rank 0 makes an id, the host layer ships its 128 bytes to every rank. */
+int pte_comm_unique_id(char id_out[128]);
+int pte_comm_init(pte_handle h, const char id[128], int rank, int n_ranks);
+/* All-gather of {n_in, n_survived, n_emitted, n_tombstones} of the last pte_run:
+ * counts[4 * n_ranks], rank-major.  The only data that crosses GPUs on this path. */
+int pte_gather_counts(pte_handle h, uint64_t* counts);
+
+/*
+ * Synthetic replay logs (shared spec of pte_generate, pte_generate_host and oracle/oracle.c).
+ * All integer; mix64 is the splitmix64 finaliser.  For local event j of shard g of G:
+ *   e   = j*G + g                      rv = e + 1
+ *   r1  = mix64(seed ^ mix64(e + 0x9E3779B97F4A7C15)), r2 = mix64(r1 + 0xD1B54A32D192ED03),
+ *   r3  = mix64(r2 + 0x8CB92BA72F3D8DD7),              r4 = mix64(r3 + 0x2545F4914F6CDD1D)
+ *   q   = mulhi64(r1, n_pods)                                        (dist 0)
+ *       = ((2^o - 1 + (r2 & (2^o - 1))) mod n_pods * 2654435761 + 40503) mod n_pods,
+ *         o = mulhi64(r1, bitlen(n_pods))                            (dist 1)
+ *   pod = q*G + g    uid_hi = mix64(pod ^ 0x6B38735F77617463)  uid_lo = mix64(~pod ^ 0x5F62323030706F64)
+ *   ns_id = pod mod 5    phase = ((r3 & 0xFFFFFFFF) * 5) >> 32, overridden by NOSTATUS if
+ *   (r4 & 0xFFFFFF) < p_nostatus_q24, else by NULL if ((r4 >> 24) & 0xFFFFFF) < p_null_q24
+ *   draw = (r3 >> 40) < p_del_q24
+ *   type = ADDED if the pod has no earlier event or its previous event had draw set,
+ *          else DELETED if draw, else MODIFIED.
+ */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTE_H */

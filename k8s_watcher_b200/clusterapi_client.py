@@ -1,0 +1,115 @@
+"""Sink side of the watcher: same surface as the reference's ClusterApiClient
+(watcher/clusterapi_client.py:6-61), plus a batched call for the bulk engine.
+
+There is no network where this runs, so the default transport is an in-memory
+mock that records every request body and answers 200.  ``transport`` may be any
+callable ``(method, url, body_bytes_or_None, headers, timeout) -> status_code``;
+:func:`requests_transport` gives the reference's real behaviour.
+"""
+from __future__ import annotations
+
+import json
+import logging
+from typing import Any, Callable, Dict, List, Optional
+
+
+class ConnectionFailed(Exception):
+    """Raised by a transport that cannot reach the server."""
+
+
+class RequestTimeout(Exception):
+    """Raised by a transport whose request timed out."""
+
+
+class MockTransport:
+    """Records what would have gone on the wire."""
+
+    def __init__(self, status: int = 200):
+        self.status = status
+        self.requests: List[Dict[str, Any]] = []
+
+    def __call__(self, method, url, body, headers, timeout):
+        self.requests.append({"method": method, "url": url, "body": body, "headers": dict(headers)})
+        return self.status
+
+    def bodies(self) -> List[bytes]:
+        return [r["body"] for r in self.requests if r["method"] == "POST"]
+
+
+def requests_transport():
+    """Transport over ``requests.Session`` (what the reference uses, clusterapi_client.py:9,36,58)."""
+    import requests
+    session = requests.Session()
+
+    def send(method, url, body, headers, timeout):
+        try:
+            r = session.request(method, url, data=body, headers=headers, timeout=timeout)
+        except requests.exceptions.ConnectionError as e:
+            raise ConnectionFailed(str(e))
+        except requests.exceptions.Timeout as e:
+            raise RequestTimeout(str(e))
+        return r.status_code
+    return send
+
+
+def wire_body(pod_data: Dict[str, Any]) -> bytes:
+    """Bytes ``requests`` puts on the wire for ``session.post(endpoint, json=pod_data)``:
+    ``json.dumps(pod_data, allow_nan=False)`` in insertion order, UTF-8 encoded."""
+    return json.dumps(pod_data, allow_nan=False).encode("utf-8")
+
+
+class ClusterApiClient:
+    def __init__(self, base_url: str, api_key: Optional[str] = None, *, transport: Optional[Callable] = None):
+        self.base_url = base_url.rstrip("/")
+        self.api_key = api_key
+        self.transport = transport if transport is not None else MockTransport()
+        self.session = self.transport            # the reference exposes .session; keep the name alive
+        self.logger = logging.getLogger(__name__)
+        self.headers: Dict[str, str] = {}
+        if self.api_key:                          # clusterapi_client.py:14-18
+            self.headers = {"Authorization": "Bearer %s" % self.api_key, "Content-Type": "application/json"}
+
+    def _post_body(self, endpoint: str, body: bytes, name: str) -> bool:
+        try:
+            status = self.transport("POST", endpoint, body, self.headers, None)
+            if status == 200:
+                self.logger.info("Successfully updated pod data for %s", name)
+                return True
+            self.logger.error("Failed to update pod data. Status: %s", status)
+            return False
+        except ConnectionFailed:
+            self.logger.error("Connection error: Unable to connect to clusterapi at %s", endpoint)
+            return False
+        except RequestTimeout:
+            self.logger.error("Timeout error: Request to %s timed out", endpoint)
+            return False
+        except Exception as e:                    # clusterapi_client.py:51-53: never raise
+            self.logger.error("Unexpected error calling clusterapi: %s", e)
+            return False
+
+    def update_pod_status(self, pod_data: Dict[str, Any]) -> bool:
+        """POST one payload to ``{base}/api/pods/update``; True iff the answer is 200
+        (clusterapi_client.py:20-53)."""
+        endpoint = "%s/api/pods/update" % self.base_url
+        self.logger.info("Calling clusterapi: %s", endpoint)
+        try:
+            body = wire_body(pod_data)
+        except Exception as e:
+            self.logger.error("Unexpected error calling clusterapi: %s", e)
+            return False
+        return self._post_body(endpoint, body, pod_data.get("name", "unknown"))
+
+    def update_pod_status_batch(self, batch, event_timestamp: Optional[str] = None) -> int:
+        """Hand every emitted record of ``batch`` to the sink, in replay order.
+        Returns the number of successful updates."""
+        ok = 0
+        for payload in batch.payloads(event_timestamp=event_timestamp):
+            ok += bool(self.update_pod_status(payload))
+        return ok
+
+    def health_check(self) -> bool:
+        """GET ``{base}/health`` with a 5 s timeout (clusterapi_client.py:55-61)."""
+        try:
+            return self.transport("GET", "%s/health" % self.base_url, None, self.headers, 5) == 200
+        except Exception:
+            return False

@@ -1,0 +1,652 @@
+// Host side of libpte.so: device memory, kernel sequencing and the C ABI of include/pte.h.
+// The path it runs in bulk is the reference's per-event loop, watcher/pod_watcher.py:266-269
+// -> handle_pod_event (:214-241), plus the last-known-phase layer of SURVEY.md 8a row 7.
+#include "../../include/pte.h"
+#include "pte_kernels.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+constexpr u64 kPad = 8192;                       // every per-event buffer is padded to this many elements
+constexpr u64 kMaxEvents = (1ull << 30) - 1;     // look-back words carry 30-bit counts
+
+inline u64 round_up(u64 x, u64 m) { return (x + m - 1) / m * m; }
+inline u32 bitlen_host(u64 x) { u32 n = 0; while (x) { n++; x >>= 1; } return n; }
+
+// radix pass configurations (threads, records per thread); PTE_PASS_CFG picks one for tuning runs
+struct PassCfg { int threads, items; };
+constexpr PassCfg kPassCfgs[] = {{256, 16}, {512, 8}, {384, 12}, {256, 8}, {512, 12}};
+constexpr int kNumPassCfgs = sizeof(kPassCfgs) / sizeof(kPassCfgs[0]);
+
+template <int T, int I>
+cudaError_t launch_pass(int grid, cudaStream_t st, const u64* in, u64* out, const u64* n_ptr, u64 n_fixed, int shift,
+                        u32 mask, const u32* hist, u32* lookback, u32* ticket) {
+    size_t smem = sizeof(RadixPassSmem<T, I>);
+    radix_pass_kernel<T, I><<<grid, T, smem, st>>>(in, out, n_ptr, n_fixed, shift, mask, hist, lookback, ticket);
+    return cudaGetLastError();
+}
+template <int T, int I>
+cudaError_t prepare_pass(int* occ) {
+    size_t smem = sizeof(RadixPassSmem<T, I>);
+    cudaError_t e = cudaFuncSetAttribute(radix_pass_kernel<T, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, radix_pass_kernel<T, I>, T, smem);
+}
+
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool load(std::string& err) {
+        if (lib) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) { lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+        if (!lib) { err = std::string("dlopen libnccl failed: ") + dlerror(); return false; }
+        GetUniqueId = (decltype(GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+        CommInitRank = (decltype(CommInitRank))dlsym(lib, "ncclCommInitRank");
+        AllGather = (decltype(AllGather))dlsym(lib, "ncclAllGather");
+        CommDestroy = (decltype(CommDestroy))dlsym(lib, "ncclCommDestroy");
+        GetErrorString = (decltype(GetErrorString))dlsym(lib, "ncclGetErrorString");
+        if (!GetUniqueId || !CommInitRank || !AllGather || !CommDestroy || !GetErrorString) {
+            err = "libnccl is missing an expected symbol"; return false;
+        }
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+}  // namespace
+
+struct pte_engine {
+    int device = 0, num_sms = 0;
+    u64 max_events = 0, max_pods = 0, cap_ev = 0;
+    cudaStream_t stream = nullptr;
+    // the log
+    u64 *uid_hi = nullptr, *uid_lo = nullptr, *rv = nullptr;
+    u32* ns = nullptr;
+    u8 *phase = nullptr, *type = nullptr;
+    u64 n_events = 0;
+    // interning dictionary
+    Slot* table = nullptr;
+    u64 table_cap = 0;
+    RecLayout L{};
+    // sort
+    u64 *recA = nullptr, *recB = nullptr;
+    u32 *lookback = nullptr, *hist = nullptr;
+    u64 lookback_words = 0;
+    int pass_cfg = 0, pass_occ = 1, pass_tile = 4096;
+    Counters* ctr = nullptr;
+    // filters
+    u32* ns_bitmap = nullptr;
+    u32 ns_words = 0;
+    int ns_filter_on = 0, critical_only = 0;
+    // outputs
+    u32 *out_idx = nullptr, *out_ns = nullptr;
+    u64 *out_rv = nullptr, *out_key = nullptr;
+    u8 *out_phase = nullptr, *out_type = nullptr;
+    bool has_run = false;
+    Counters last{};
+    // timing
+    std::vector<cudaEvent_t> ev;
+    u32 n_launches = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pass_ev;
+    size_t pass_ev_used = 0;
+    // multi-GPU
+    ncclComm_t comm = nullptr;
+    int rank = 0, n_ranks = 1;
+    u64 *d_counts_send = nullptr, *d_counts_recv = nullptr;
+    std::string err;
+};
+
+#define FAIL(h, code, msg)                                  \
+    do {                                                    \
+        std::string m__ = (msg);                            \
+        if (h) (h)->err = m__; else g_err = m__;            \
+        return (code);                                      \
+    } while (0)
+
+#define CK(h, call)                                                                                         \
+    do {                                                                                                    \
+        cudaError_t e__ = (call);                                                                           \
+        if (e__ != cudaSuccess)                                                                             \
+            FAIL(h, PTE_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));                      \
+    } while (0)
+
+namespace {
+
+int launch_pass_cfg(pte_engine* h, const u64* in, u64* out, const u64* n_ptr, u64 n_fixed, int shift, u32 mask,
+                    const u32* hist) {
+    int grid = h->num_sms * h->pass_occ;
+    u32* ticket = &h->ctr->ticket[1];
+    cudaError_t e;
+    switch (h->pass_cfg) {
+        case 1: e = launch_pass<512, 8>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+        case 2: e = launch_pass<384, 12>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+        case 3: e = launch_pass<256, 8>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+        case 4: e = launch_pass<512, 12>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+        default: e = launch_pass<256, 16>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+    }
+    if (e != cudaSuccess) FAIL(h, PTE_ERR_CUDA, std::string("radix_pass_kernel: ") + cudaGetErrorString(e));
+    h->n_launches++;
+    return PTE_OK;
+}
+
+int prepare_pass_cfg(pte_engine* h) {
+    cudaError_t e;
+    switch (h->pass_cfg) {
+        case 1: e = prepare_pass<512, 8>(&h->pass_occ); break;
+        case 2: e = prepare_pass<384, 12>(&h->pass_occ); break;
+        case 3: e = prepare_pass<256, 8>(&h->pass_occ); break;
+        case 4: e = prepare_pass<512, 12>(&h->pass_occ); break;
+        default: e = prepare_pass<256, 16>(&h->pass_occ); break;
+    }
+    if (e != cudaSuccess) FAIL(h, PTE_ERR_CUDA, std::string("radix pass set-up: ") + cudaGetErrorString(e));
+    if (h->pass_occ < 1) FAIL(h, PTE_ERR_CUDA, "radix pass does not fit on an SM");
+    h->pass_tile = kPassCfgs[h->pass_cfg].threads * kPassCfgs[h->pass_cfg].items;
+    return PTE_OK;
+}
+
+// Stable LSD sort of the records in `src` on bits [bit_lo, bit_hi); `other` is the ping-pong buffer.
+// n is read on the device from n_ptr when given (n_upper bounds it for sizing), else n_upper.
+// On return *result points at the buffer that holds the sorted records.
+int sort_field(pte_engine* h, u64* src, u64* other, const u64* n_ptr, u64 n_upper, int bit_lo, int bit_hi,
+               u64** result) {
+    *result = src;
+    if (bit_hi <= bit_lo || n_upper == 0) return PTE_OK;
+    const int passes = (bit_hi - bit_lo + 7) / 8;
+    if (passes > kMaxPasses) FAIL(h, PTE_ERR_INVALID, "sort field wider than 64 bits");
+    CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, h->stream));
+    int hgrid = (int)std::min<u64>((u64)h->num_sms * 8, (n_upper + 511) / 512);
+    radix_hist_kernel<256><<<std::max(hgrid, 1), 256, 0, h->stream>>>(src, n_ptr, n_upper, bit_lo, passes, bit_hi, h->hist);
+    CK(h, cudaGetLastError());
+    h->n_launches++;
+    const u64 tiles = (n_upper + h->pass_tile - 1) / h->pass_tile;
+    if (tiles * kRadix > h->lookback_words) FAIL(h, PTE_ERR_CAPACITY, "look-back buffer too small");
+    u64 *a = src, *b = other;
+    for (int p = 0; p < passes; p++) {
+        const int shift = bit_lo + 8 * p;
+        const int rem = bit_hi - shift;
+        const u32 mask = rem >= 8 ? 0xFFu : ((1u << rem) - 1);
+        CK(h, cudaMemsetAsync(h->lookback, 0, tiles * kRadix * sizeof(u32), h->stream));
+        CK(h, cudaMemsetAsync(&h->ctr->ticket[1], 0, sizeof(u32), h->stream));
+        if (h->pass_ev_used == h->pass_ev.size()) {
+            cudaEvent_t e0, e1;
+            CK(h, cudaEventCreate(&e0));
+            CK(h, cudaEventCreate(&e1));
+            h->pass_ev.emplace_back(e0, e1);
+        }
+        auto& pe = h->pass_ev[h->pass_ev_used++];
+        CK(h, cudaEventRecord(pe.first, h->stream));
+        int rc = launch_pass_cfg(h, a, b, n_ptr, n_upper, shift, mask, h->hist + p * kRadix);
+        if (rc) return rc;
+        CK(h, cudaEventRecord(pe.second, h->stream));
+        std::swap(a, b);
+    }
+    *result = a;
+    return PTE_OK;
+}
+
+template <typename T>
+int dev_alloc(pte_engine* h, T** p, u64 count) {
+    CK(h, cudaMalloc((void**)p, count * sizeof(T)));
+    return PTE_OK;
+}
+
+int check_flags(pte_engine* h, u32 flags) {
+    if (flags & kFlagBadEvent)
+        FAIL(h, PTE_ERR_BAD_EVENT, "log holds an event with type not in {ADDED,MODIFIED,DELETED}, phase code > 62 or uid 0:0");
+    if (flags & kFlagTableFull)
+        FAIL(h, PTE_ERR_TABLE_FULL, "more distinct uids than the engine was created for (max_pods)");
+    if (flags & kFlagUnordered)
+        FAIL(h, PTE_ERR_UNORDERED, "resourceVersion decreases along arrival order; sort the log by rv before ingest");
+    return PTE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pte_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* pte_last_error(pte_handle h) { return h ? h->err.c_str() : g_err.c_str(); }
+
+void pte_destroy(pte_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->lookback,
+                    h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
+                    h->out_type, h->d_counts_send, h->d_counts_recv};
+    for (void* b : bufs) if (b) cudaFree(b);
+    for (auto e : h->ev) cudaEventDestroy(e);
+    for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* out) {
+    if (!out) FAIL((pte_handle) nullptr, PTE_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int ndev = pte_device_count();
+    if (ndev <= 0) FAIL((pte_handle) nullptr, PTE_ERR_NO_DEVICE, "no CUDA device: the engine has no CPU path");
+    if (device < 0 || device >= ndev) FAIL((pte_handle) nullptr, PTE_ERR_INVALID, "device index out of range");
+    if (max_events == 0) max_events = 1;
+    if (max_events > kMaxEvents)
+        FAIL((pte_handle) nullptr, PTE_ERR_CAPACITY, "max_events above 2^30-1 per engine: shard the log by uid");
+    if (max_pods == 0 || max_pods > max_events) max_pods = max_events;
+
+    pte_engine* h = new pte_engine();
+    h->device = device; h->max_events = max_events; h->max_pods = max_pods;
+    u64 want = (u64)((double)max_pods / 0.6) + 1;
+    u64 cap = 256;
+    while (cap < want) cap <<= 1;
+    h->table_cap = cap;
+    h->L.idx_bits = std::max<u32>(1, bitlen_host(max_events - 1));
+    h->L.key_bits = bitlen_host(cap - 1);
+    if (8 + h->L.idx_bits + h->L.key_bits > 64) {
+        g_err = "record layout does not fit 64 bits (idx_bits + key_bits > 56): lower max_events or max_pods";
+        delete h;
+        return PTE_ERR_CAPACITY;
+    }
+    const char* cfg = getenv("PTE_PASS_CFG");
+    if (cfg) h->pass_cfg = std::min(std::max(atoi(cfg), 0), kNumPassCfgs - 1);
+
+#define CKC(call)                                                                      \
+    do {                                                                               \
+        int rc__ = (call);                                                             \
+        if (rc__ != PTE_OK) { g_err = h->err; pte_destroy(h); return rc__; }           \
+    } while (0)
+#define CKCU(call)                                                                     \
+    do {                                                                               \
+        cudaError_t e__ = (call);                                                      \
+        if (e__ != cudaSuccess) {                                                      \
+            g_err = std::string(#call) + ": " + cudaGetErrorString(e__);               \
+            pte_destroy(h);                                                            \
+            return PTE_ERR_CUDA;                                                       \
+        }                                                                              \
+    } while (0)
+
+    CKCU(cudaSetDevice(device));
+    CKCU(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    CKCU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CKC(prepare_pass_cfg(h));
+    h->cap_ev = round_up(max_events, kPad) + kPad;
+    const u64 c = h->cap_ev;
+    CKC(dev_alloc(h, &h->uid_hi, c)); CKC(dev_alloc(h, &h->uid_lo, c)); CKC(dev_alloc(h, &h->rv, c));
+    CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
+    CKC(dev_alloc(h, &h->table, h->table_cap));
+    CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c));
+    // look-back words: one per (radix tile, digit); also one per intern tile
+    u64 min_tile = 2048;
+    h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
+    CKC(dev_alloc(h, &h->lookback, h->lookback_words));
+    CKC(dev_alloc(h, &h->hist, (u64)kMaxPasses * kRadix));
+    CKC(dev_alloc(h, &h->ctr, 1));
+    CKC(dev_alloc(h, &h->out_idx, c)); CKC(dev_alloc(h, &h->out_ns, c));
+    CKC(dev_alloc(h, &h->out_rv, c)); CKC(dev_alloc(h, &h->out_key, c));
+    CKC(dev_alloc(h, &h->out_phase, c)); CKC(dev_alloc(h, &h->out_type, c));
+    CKC(dev_alloc(h, &h->d_counts_send, 4));
+    CKCU(cudaMemsetAsync(h->ctr, 0, sizeof(Counters), h->stream));
+    // pads must be readable garbage-free for the vector loads past n
+    CKCU(cudaMemsetAsync(h->rv, 0, c * sizeof(u64), h->stream));
+    for (int i = 0; i < 8; i++) { cudaEvent_t e; CKCU(cudaEventCreate(&e)); h->ev.push_back(e); }
+    CKCU(cudaStreamSynchronize(h->stream));
+#undef CKC
+#undef CKCU
+    *out = h;
+    return PTE_OK;
+}
+
+int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_filter_on, int production_critical_only) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (n_allow < 0 || (n_allow > 0 && !ns_allow)) FAIL(h, PTE_ERR_INVALID, "bad namespace allow-list");
+    CK(h, cudaSetDevice(h->device));
+    u32 max_id = 0;
+    for (int i = 0; i < n_allow; i++) max_id = std::max(max_id, ns_allow[i]);
+    u32 words = n_allow ? max_id / 32 + 1 : 1;
+    std::vector<u32> bm(words, 0u);
+    for (int i = 0; i < n_allow; i++) bm[ns_allow[i] >> 5] |= 1u << (ns_allow[i] & 31);
+    if (h->ns_bitmap) { CK(h, cudaStreamSynchronize(h->stream)); CK(h, cudaFree(h->ns_bitmap)); h->ns_bitmap = nullptr; }
+    CK(h, cudaMalloc((void**)&h->ns_bitmap, words * sizeof(u32)));
+    CK(h, cudaMemcpy(h->ns_bitmap, bm.data(), words * sizeof(u32), cudaMemcpyHostToDevice));
+    h->ns_words = words;
+    h->ns_filter_on = (n_allow > 0 || ns_filter_on) ? 1 : 0;
+    h->critical_only = production_critical_only ? 1 : 0;
+    return PTE_OK;
+}
+
+int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
+               const uint8_t* phase, const uint8_t* type, uint64_t n) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
+    if (n && (!uid_hi || !uid_lo || !rv || !ns_id || !phase || !type)) FAIL(h, PTE_ERR_INVALID, "NULL column");
+    CK(h, cudaSetDevice(h->device));
+    if (n) {
+        CK(h, cudaMemcpyAsync(h->uid_hi, uid_hi, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaMemcpyAsync(h->uid_lo, uid_lo, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaMemcpyAsync(h->rv, rv, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaMemcpyAsync(h->ns, ns_id, n * 4, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaMemcpyAsync(h->phase, phase, n, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaMemcpyAsync(h->type, type, n, cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    h->n_events = n;
+    h->has_run = false;
+    return PTE_OK;
+}
+
+int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv, uint32_t* ns_id, uint8_t* phase,
+                 uint8_t* type, uint64_t cap, uint64_t* n_out) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    const u64 n = h->n_events;
+    if (n_out) *n_out = n;
+    if (cap < n) FAIL(h, PTE_ERR_CAPACITY, "buffers smaller than the log");
+    CK(h, cudaSetDevice(h->device));
+    if (n) {
+        if (uid_hi) CK(h, cudaMemcpyAsync(uid_hi, h->uid_hi, n * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (uid_lo) CK(h, cudaMemcpyAsync(uid_lo, h->uid_lo, n * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (rv) CK(h, cudaMemcpyAsync(rv, h->rv, n * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (ns_id) CK(h, cudaMemcpyAsync(ns_id, h->ns, n * 4, cudaMemcpyDeviceToHost, h->stream));
+        if (phase) CK(h, cudaMemcpyAsync(phase, h->phase, n, cudaMemcpyDeviceToHost, h->stream));
+        if (type) CK(h, cudaMemcpyAsync(type, h->type, n, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    return PTE_OK;
+}
+
+static int check_gen(const pte_gen_params* p, std::string& why) {
+    if (!p) { why = "params are NULL"; return PTE_ERR_INVALID; }
+    if (p->n_shards == 0 || p->shard >= p->n_shards) { why = "shard must be in [0, n_shards)"; return PTE_ERR_INVALID; }
+    if (p->n_events && p->n_pods == 0) { why = "n_pods must be > 0"; return PTE_ERR_INVALID; }
+    if (p->dist > 1) { why = "dist must be 0 (uniform) or 1 (octave-Zipf)"; return PTE_ERR_INVALID; }
+    if (p->n_pods >= (1ull << 32)) { why = "n_pods must be below 2^32"; return PTE_ERR_INVALID; }
+    return PTE_OK;
+}
+
+static GenParams to_gen(const pte_gen_params* p) {
+    GenParams g;
+    g.seed = p->seed; g.n_events = p->n_events; g.n_pods = p->n_pods; g.dist = p->dist;
+    g.p_del_q24 = p->p_del_q24; g.p_nostatus_q24 = p->p_nostatus_q24; g.p_null_q24 = p->p_null_q24;
+    g.shard = p->shard; g.n_shards = p->n_shards;
+    return g;
+}
+
+int pte_generate_host(const pte_gen_params* p, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv, uint32_t* ns_id,
+                      uint8_t* phase, uint8_t* type) {
+    std::string why;
+    int rc = check_gen(p, why);
+    if (rc) FAIL((pte_handle) nullptr, rc, why);
+    GenParams g = to_gen(p);
+    // per-pod state: 0 no event yet, 1 previous event had no delete draw, 2 it had one
+    std::vector<u8> st(g.n_pods ? g.n_pods : 1, 0);
+    for (u64 j = 0; j < g.n_events; j++) {
+        GenEvent e = gen_event(g, j);
+        u8 s = st[e.q];
+        if (uid_hi) uid_hi[j] = e.uid_hi;
+        if (uid_lo) uid_lo[j] = e.uid_lo;
+        if (rv) rv[j] = e.rv;
+        if (ns_id) ns_id[j] = e.ns;
+        if (phase) phase[j] = (u8)e.phase;
+        if (type) type[j] = (u8)gen_type(s != 0, s == 2, e.draw);
+        st[e.q] = e.draw ? 2 : 1;
+    }
+    return PTE_OK;
+}
+
+int pte_generate(pte_handle h, const pte_gen_params* p) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    std::string why;
+    int rc = check_gen(p, why);
+    if (rc) FAIL(h, rc, why);
+    if (p->n_events > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "n_events above the engine's max_events");
+    CK(h, cudaSetDevice(h->device));
+    GenArgs a;
+    a.g = to_gen(p);
+    a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
+    a.rec_out = h->recA;
+    a.L.idx_bits = h->L.idx_bits;
+    a.L.key_bits = std::max<u32>(1, bitlen_host(p->n_pods ? p->n_pods - 1 : 0));
+    if (8 + a.L.idx_bits + a.L.key_bits > 64) FAIL(h, PTE_ERR_CAPACITY, "n_pods too large for the generator's sort record");
+    const u64 n = p->n_events;
+    h->n_events = n;
+    h->has_run = false;
+    if (n == 0) return PTE_OK;
+    int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+    gen_fill_kernel<<<grid, 256, 0, h->stream>>>(a);
+    CK(h, cudaGetLastError());
+    u64* sorted = nullptr;
+    h->pass_ev_used = 0;
+    rc = sort_field(h, h->recA, h->recB, nullptr, n, a.L.key_shift(), a.L.key_shift() + a.L.key_bits, &sorted);
+    if (rc) return rc;
+    gen_type_kernel<<<grid, 256, 0, h->stream>>>(sorted, n, a.L, h->type);
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    return PTE_OK;
+}
+
+int pte_run(pte_handle h, int dedupe, pte_stats* out) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    CK(h, cudaSetDevice(h->device));
+    const u64 n = h->n_events;
+    h->n_launches = 0;
+    h->pass_ev_used = 0;
+    h->has_run = false;
+    cudaStream_t st = h->stream;
+    CK(h, cudaEventRecord(h->ev[0], st));
+    CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
+    CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
+    const bool filtered = h->critical_only || h->ns_filter_on;
+    u64* final_rec = h->recA;
+    if (n) {
+        InternArgs a;
+        a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
+        a.n = n; a.table = h->table; a.table_mask = (u32)(h->table_cap - 1); a.L = h->L; a.rec_out = h->recA;
+        a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
+        a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
+        const u64 tiles = (n + kInternTile - 1) / kInternTile;
+        int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
+        if (filtered) {
+            CK(h, cudaMemsetAsync(h->lookback, 0, tiles * sizeof(u32), st));
+            intern_pack_kernel<true><<<grid, kInternThreads, 0, st>>>(a);
+        } else {
+            intern_pack_kernel<false><<<grid, kInternThreads, 0, st>>>(a);
+        }
+        CK(h, cudaGetLastError());
+        h->n_launches++;
+    }
+    CK(h, cudaEventRecord(h->ev[1], st));
+    if (n && dedupe) {
+        u64* sorted = nullptr;
+        int rc = sort_field(h, h->recA, h->recB, &h->ctr->n_survived, n, h->L.key_shift(),
+                            h->L.key_shift() + h->L.key_bits, &sorted);
+        if (rc) return rc;
+        CK(h, cudaEventRecord(h->ev[2], st));
+        u64* other = sorted == h->recA ? h->recB : h->recA;
+        int grid = (int)std::min<u64>((n + kDiffThreads * kDiffItems - 1) / (kDiffThreads * kDiffItems), (u64)h->num_sms * 8);
+        diff_compact_kernel<<<grid, kDiffThreads, 0, st>>>(sorted, other, h->L, h->ctr);
+        CK(h, cudaGetLastError());
+        h->n_launches++;
+        CK(h, cudaEventRecord(h->ev[3], st));
+        rc = sort_field(h, other, sorted, &h->ctr->n_emitted, n, 8, 8 + h->L.idx_bits, &final_rec);
+        if (rc) return rc;
+        CK(h, cudaEventRecord(h->ev[4], st));
+    } else {
+        // R-trace: every survivor is emitted, already in replay order
+        CK(h, cudaEventRecord(h->ev[2], st));
+        CK(h, cudaMemcpyAsync(&h->ctr->n_emitted, &h->ctr->n_survived, sizeof(u64), cudaMemcpyDeviceToDevice, st));
+        CK(h, cudaMemcpyAsync(&h->ctr->n_tombstones, &h->ctr->n_del_survived, sizeof(u64), cudaMemcpyDeviceToDevice, st));
+        CK(h, cudaEventRecord(h->ev[3], st));
+        CK(h, cudaEventRecord(h->ev[4], st));
+    }
+    if (n) {
+        AssembleArgs a;
+        a.rec = final_rec; a.n_ptr = &h->ctr->n_emitted; a.rv = h->rv; a.ns = h->ns; a.L = h->L;
+        a.out_idx = h->out_idx; a.out_rv = h->out_rv; a.out_key = h->out_key; a.out_ns = h->out_ns;
+        a.out_phase = h->out_phase; a.out_type = h->out_type;
+        int grid = (int)std::min<u64>((n + 1023) / 1024, (u64)h->num_sms * 8);
+        assemble_kernel<<<grid, 256, 0, st>>>(a);
+        CK(h, cudaGetLastError());
+        h->n_launches++;
+    }
+    CK(h, cudaEventRecord(h->ev[5], st));
+    CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    int rc = check_flags(h, h->last.flags);
+    if (rc) return rc;
+    h->has_run = true;
+    if (out) {
+        memset(out, 0, sizeof(*out));
+        out->n_in = n; out->n_survived = h->last.n_survived; out->n_emitted = h->last.n_emitted;
+        out->n_tombstones = h->last.n_tombstones; out->n_pods = h->last.n_pods;
+        out->ordered = 1; out->n_launches = h->n_launches;
+        cudaEventElapsedTime(&out->ms_total, h->ev[0], h->ev[5]);
+        cudaEventElapsedTime(&out->ms_intern, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&out->ms_sort_key, h->ev[1], h->ev[2]);
+        cudaEventElapsedTime(&out->ms_diff, h->ev[2], h->ev[3]);
+        cudaEventElapsedTime(&out->ms_sort_order, h->ev[3], h->ev[4]);
+        cudaEventElapsedTime(&out->ms_assemble, h->ev[4], h->ev[5]);
+        float sum = 0;
+        for (size_t i = 0; i < h->pass_ev_used; i++) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, h->pass_ev[i].first, h->pass_ev[i].second);
+            sum += ms;
+        }
+        out->n_passes = (u32)h->pass_ev_used;
+        out->ms_pass_avg = h->pass_ev_used ? sum / h->pass_ev_used : 0.f;
+    }
+    return PTE_OK;
+}
+
+int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t* ns_id, uint8_t* phase, uint8_t* type,
+              uint64_t cap, uint64_t* n_out) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_fetch before a successful pte_run");
+    const u64 n = h->last.n_emitted;
+    if (n_out) *n_out = n;
+    if (cap < n) FAIL(h, PTE_ERR_CAPACITY, "buffers smaller than the emitted record count");
+    CK(h, cudaSetDevice(h->device));
+    if (n) {
+        cudaStream_t st = h->stream;
+        if (idx) CK(h, cudaMemcpyAsync(idx, h->out_idx, n * 4, cudaMemcpyDeviceToHost, st));
+        if (rv) CK(h, cudaMemcpyAsync(rv, h->out_rv, n * 8, cudaMemcpyDeviceToHost, st));
+        if (key) CK(h, cudaMemcpyAsync(key, h->out_key, n * 8, cudaMemcpyDeviceToHost, st));
+        if (ns_id) CK(h, cudaMemcpyAsync(ns_id, h->out_ns, n * 4, cudaMemcpyDeviceToHost, st));
+        if (phase) CK(h, cudaMemcpyAsync(phase, h->out_phase, n, cudaMemcpyDeviceToHost, st));
+        if (type) CK(h, cudaMemcpyAsync(type, h->out_type, n, cudaMemcpyDeviceToHost, st));
+        CK(h, cudaStreamSynchronize(st));
+    }
+    return PTE_OK;
+}
+
+int pte_digest(pte_handle h, uint64_t* out) {
+    if (!h || !out) FAIL(h, PTE_ERR_INVALID, "NULL argument");
+    if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_digest before a successful pte_run");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemsetAsync(&h->ctr->digest, 0, sizeof(u64), h->stream));
+    const u64 n = h->last.n_emitted;
+    if (n) {
+        int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+        digest_kernel<<<grid, 256, 0, h->stream>>>(h->out_idx, h->out_phase, h->out_type, h->uid_hi, h->uid_lo, h->rv,
+                                                    h->ns, h->ctr);
+        CK(h, cudaGetLastError());
+    }
+    u64 d = 0;
+    CK(h, cudaMemcpyAsync(&d, &h->ctr->digest, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    *out = d;
+    return PTE_OK;
+}
+
+void* pte_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        g_err = "cudaHostAlloc failed";
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void pte_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+uint32_t pte_shard_of(uint64_t uid_hi, uint64_t uid_lo, uint32_t n_shards) {
+    (void)uid_lo;
+    return n_shards ? shard_of_uid(uid_hi, n_shards) : 0;
+}
+
+int pte_debug_sort_u64(pte_handle h, uint64_t* records, uint64_t n, int bit_lo, int bit_hi) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "more records than the engine's max_events");
+    if (bit_lo < 0 || bit_hi > 64 || bit_hi < bit_lo) FAIL(h, PTE_ERR_INVALID, "bad bit range");
+    if (n == 0) return PTE_OK;
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemcpyAsync(h->recA, records, n * 8, cudaMemcpyHostToDevice, h->stream));
+    u64* sorted = nullptr;
+    h->pass_ev_used = 0;
+    int rc = sort_field(h, h->recA, h->recB, nullptr, n, bit_lo, bit_hi, &sorted);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(records, sorted, n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->has_run = false;
+    return PTE_OK;
+}
+
+int pte_comm_unique_id(char id_out[128]) {
+    if (!id_out) FAIL((pte_handle) nullptr, PTE_ERR_INVALID, "id_out is NULL");
+    if (!g_nccl.load(g_err)) return PTE_ERR_NCCL;
+    ncclUniqueId id;
+    ncclResult_t r = g_nccl.GetUniqueId(&id);
+    if (r != ncclSuccess) FAIL((pte_handle) nullptr, PTE_ERR_NCCL, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(id_out, &id, 128);
+    return PTE_OK;
+}
+
+int pte_comm_init(pte_handle h, const char id[128], int rank, int n_ranks) {
+    if (!h || !id) FAIL(h, PTE_ERR_INVALID, "NULL argument");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) FAIL(h, PTE_ERR_INVALID, "rank must be in [0, n_ranks)");
+    if (!g_nccl.load(h->err)) return PTE_ERR_NCCL;
+    CK(h, cudaSetDevice(h->device));
+    ncclUniqueId uid;
+    memcpy(&uid, id, 128);
+    ncclResult_t r = g_nccl.CommInitRank(&h->comm, n_ranks, uid, rank);
+    if (r != ncclSuccess) FAIL(h, PTE_ERR_NCCL, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
+    h->rank = rank; h->n_ranks = n_ranks;
+    if (h->d_counts_recv) { cudaFree(h->d_counts_recv); h->d_counts_recv = nullptr; }
+    CK(h, cudaMalloc((void**)&h->d_counts_recv, sizeof(u64) * 4 * n_ranks));
+    return PTE_OK;
+}
+
+int pte_gather_counts(pte_handle h, uint64_t* counts) {
+    if (!h || !counts) FAIL(h, PTE_ERR_INVALID, "NULL argument");
+    if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_gather_counts before a successful pte_run");
+    u64 mine[4] = {h->n_events, h->last.n_survived, h->last.n_emitted, h->last.n_tombstones};
+    if (h->n_ranks == 1 && !h->comm) { memcpy(counts, mine, sizeof(mine)); return PTE_OK; }
+    if (!h->comm) FAIL(h, PTE_ERR_STATE, "pte_comm_init has not been called");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemcpyAsync(h->d_counts_send, mine, sizeof(mine), cudaMemcpyHostToDevice, h->stream));
+    ncclResult_t r = g_nccl.AllGather(h->d_counts_send, h->d_counts_recv, 4, ncclUint64, h->comm, h->stream);
+    if (r != ncclSuccess) FAIL(h, PTE_ERR_NCCL, std::string("ncclAllGather: ") + g_nccl.GetErrorString(r));
+    CK(h, cudaMemcpyAsync(counts, h->d_counts_recv, sizeof(u64) * 4 * h->n_ranks, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return PTE_OK;
+}
+
+}  // extern "C"

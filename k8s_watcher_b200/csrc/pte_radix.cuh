@@ -1,0 +1,212 @@
+// LSD radix sort of 64-bit records on an arbitrary bit field, 8 bits per pass.
+//
+//   radix_hist_kernel  one read of the records -> digit counts of every pass
+//   radix_pass_kernel  one scatter pass: read 8 B, write 8 B per record, single sweep.
+//                      Tiles are chained with a decoupled look-back over per-tile digit
+//                      counts, digits are ranked inside a warp with MATCH.ANY + popc
+//                      (stable: lower lanes first), and every tile is re-ordered in shared
+//                      memory first so that global writes are runs of consecutive records.
+//
+// No reference counterpart: the reference handles one event at a time in Python
+// (watcher/pod_watcher.py:266-269); sorting by (uid key, rv) is how the bulk engine
+// brings each pod's events together (bulk-equivalent predicate).
+#pragma once
+#include "pte_common.cuh"
+
+static constexpr int kRadix = 256;
+static constexpr int kMaxPasses = 8;
+static constexpr u32 kLbPartial = 1u << 30, kLbInclusive = 2u << 30, kLbValue = (1u << 30) - 1;
+
+__device__ __forceinline__ u32 ld_relaxed_u32(const u32* p) {
+    u32 v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(u32* p, u32 v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ u32 lanemask_lt() {
+    u32 m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// Exclusive scan of one value per thread over the first 256 threads of the block.
+// Must be called by exactly threads 0..255 (named barrier 1), `tot` = 8 words of smem.
+__device__ __forceinline__ u32 excl_scan_256(u32 v, u32* tot, u32* total_out) {
+    const u32 lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    u32 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        u32 t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) tot[w] = inc;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    u32 base = 0, all = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        u32 t = tot[k];
+        if (k < (int)w) base += t;
+        all += t;
+    }
+    if (total_out) *total_out = all;
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // tot may be reused by the caller
+    return base + inc - v;
+}
+
+// ---- digit counts for n_passes passes starting at bit shift0 (field ends at bit_hi) ----
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+radix_hist_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, u64 n_fixed, int shift0,
+                  int n_passes, int bit_hi, u32* __restrict__ hist) {
+    __shared__ u32 sh[kMaxPasses * kRadix];
+    for (int k = threadIdx.x; k < n_passes * kRadix; k += THREADS) sh[k] = 0;
+    __syncthreads();
+    const u64 n = n_ptr ? *n_ptr : n_fixed;
+    u32 masks[kMaxPasses];
+#pragma unroll
+    for (int p = 0; p < kMaxPasses; p++) {
+        int rem = bit_hi - (shift0 + 8 * p);
+        masks[p] = rem >= 8 ? 0xFFu : (rem > 0 ? (1u << rem) - 1 : 0u);
+    }
+    const u64 stride = (u64)gridDim.x * THREADS * 2;
+    for (u64 i = ((u64)blockIdx.x * THREADS + threadIdx.x) * 2; i < n; i += stride) {
+        ulonglong2 v = *reinterpret_cast<const ulonglong2*>(in + i);   // buffers are padded: i+1 is readable
+        const bool two = i + 1 < n;
+#pragma unroll
+        for (int p = 0; p < kMaxPasses; p++) {
+            if (p < n_passes) {
+                int s = shift0 + 8 * p;
+                atomicAdd(&sh[p * kRadix + ((u32)(v.x >> s) & masks[p])], 1u);
+                if (two) atomicAdd(&sh[p * kRadix + ((u32)(v.y >> s) & masks[p])], 1u);
+            }
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < n_passes * kRadix; k += THREADS)
+        if (sh[k]) atomicAdd(&hist[k], sh[k]);
+}
+
+// ---- one scatter pass ----
+template <int THREADS, int ITEMS>
+struct RadixPassSmem {
+    static constexpr int WARPS = THREADS / 32;
+    static constexpr int TILE = THREADS * ITEMS;
+    u64 stage[TILE];
+    u32 warp_hist[WARPS][kRadix];
+    u32 bin_base[kRadix];
+    u32 tile_excl[kRadix];
+    u32 dst_off[kRadix];
+    u32 tot[8];
+    u32 tile;
+};
+
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ n_ptr, u64 n_fixed,
+                  int shift, u32 mask, const u32* __restrict__ hist, u32* __restrict__ lookback,
+                  u32* __restrict__ ticket) {
+    static_assert(THREADS >= 256 && THREADS % 32 == 0, "needs one thread per digit");
+    using S = RadixPassSmem<THREADS, ITEMS>;
+    constexpr int WARPS = S::WARPS, TILE = S::TILE;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    S& s = *reinterpret_cast<S*>(smem_raw);
+
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 lt = lanemask_lt();
+    const u64 n = n_ptr ? *n_ptr : n_fixed;
+
+    if (tid < kRadix) s.bin_base[tid] = excl_scan_256(hist[tid], s.tot, nullptr);
+
+    for (;;) {
+        __syncthreads();   // previous tile fully written out; bin_base visible
+        if (tid == 0) s.tile = atomicAdd(ticket, 1u);
+        for (int k = tid; k < WARPS * kRadix; k += THREADS) (&s.warp_hist[0][0])[k] = 0;
+        __syncthreads();
+        const u32 tile = s.tile;
+        const u64 tile_base = (u64)tile * TILE;
+        if (tile_base >= n) break;
+        const u32 tile_valid = (u32)min((u64)TILE, n - tile_base);
+
+        // (1) warp-striped load: warp w owns records [w*32*ITEMS, (w+1)*32*ITEMS) of the tile
+        u64 key[ITEMS];
+        u32 rank[ITEMS];
+        const u32 wbase = warp * 32 * ITEMS + lane;
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            u32 t = wbase + k * 32;
+            key[k] = t < tile_valid ? __ldcs(in + tile_base + t) : ~0ull;
+        }
+        // (2) rank inside the warp, in record order, against the warp's private digit counters
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            const bool valid = wbase + k * 32 < tile_valid;
+            const u32 d = valid ? ((u32)(key[k] >> shift) & mask) : (u32)kRadix;
+            const u32 peers = __match_any_sync(0xffffffffu, d);
+            const u32 before = peers & lt;
+            u32 base = 0;
+            if (before == 0 && valid) {
+                base = s.warp_hist[warp][d];
+                s.warp_hist[warp][d] = base + __popc(peers);
+            }
+            __syncwarp();
+            base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
+            rank[k] = base + __popc(before);
+        }
+        __syncthreads();
+
+        // (3) per digit: counts of this tile, offsets of each warp inside the digit, publish the partial
+        u32 count = 0;
+        if (tid < kRadix) {
+            u32 run = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) {
+                u32 t = s.warp_hist[w][tid];
+                s.warp_hist[w][tid] = run;
+                run += t;
+            }
+            count = run;
+            st_relaxed_u32(lookback + (u64)tile * kRadix + tid, (tile == 0 ? kLbInclusive : kLbPartial) | count);
+            s.tile_excl[tid] = excl_scan_256(count, s.tot, nullptr);
+        }
+        __syncthreads();
+
+        // (4) re-order the tile in shared memory
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            if (wbase + k * 32 < tile_valid) {
+                const u32 d = (u32)(key[k] >> shift) & mask;
+                s.stage[s.tile_excl[d] + s.warp_hist[warp][d] + rank[k]] = key[k];
+            }
+        }
+
+        // (5) decoupled look-back: records of this digit in all earlier tiles
+        if (tid < kRadix) {
+            u32 excl = 0;
+            if (tile > 0) {
+                u32 t = tile - 1;
+                for (;;) {
+                    u32 v = ld_relaxed_u32(lookback + (u64)t * kRadix + tid);
+                    if ((v >> 30) == 0) { __nanosleep(20); continue; }
+                    excl += v & kLbValue;
+                    if ((v >> 30) == 2) break;
+                    t--;
+                }
+                st_relaxed_u32(lookback + (u64)tile * kRadix + tid, kLbInclusive | (excl + count));
+            }
+            s.dst_off[tid] = s.bin_base[tid] + excl - s.tile_excl[tid];
+        }
+        __syncthreads();
+
+        // (6) coalesced runs out to global memory
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            u32 i = tid + k * THREADS;
+            if (i < tile_valid) {
+                u64 v = s.stage[i];
+                out[s.dst_off[(u32)(v >> shift) & mask] + i] = v;
+            }
+        }
+    }
+}

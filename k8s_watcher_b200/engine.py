@@ -1,0 +1,210 @@
+"""Python face of the C ABI: one :class:`PhaseTransitionEngine` per GPU.
+
+Everything here is argument marshalling; the work happens in libpte.so
+(k8s_watcher_b200/csrc).  Without the library or without a CUDA device the
+constructor raises -- there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Iterable, Optional, Sequence
+
+import numpy as np
+
+from . import _abi
+from ._abi import PteError, PteGenParams, PteStats  # noqa: F401  (re-exported)
+
+COLUMNS = (("uid_hi", np.uint64), ("uid_lo", np.uint64), ("rv", np.uint64),
+           ("ns_id", np.uint32), ("phase", np.uint8), ("type", np.uint8))
+
+
+def q24(p: float) -> int:
+    return int(round(float(p) * (1 << 24)))
+
+
+def gen_params(seed: int, n_events: int, n_pods: int, *, dist: int = 0, p_del: float = 0.0, p_nostatus: float = 0.0,
+               p_null: float = 0.0, shard: int = 0, n_shards: int = 1) -> PteGenParams:
+    return PteGenParams(seed & 0xFFFFFFFFFFFFFFFF, n_events, n_pods, dist, q24(p_del), q24(p_nostatus), q24(p_null),
+                        shard, n_shards)
+
+
+def _ptr(a: Optional[np.ndarray], ctype):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ctype))
+
+
+def generate_host(seed: int, n_events: int, n_pods: int, **kw) -> Dict[str, np.ndarray]:
+    """The synthetic replay log of include/pte.h, generated on the host by libpte.so."""
+    cols = {name: np.empty(n_events, dt) for name, dt in COLUMNS}
+    p = gen_params(seed, n_events, n_pods, **kw)
+    rc = _abi.lib().pte_generate_host(C.byref(p), _ptr(cols["uid_hi"], C.c_uint64), _ptr(cols["uid_lo"], C.c_uint64),
+                                      _ptr(cols["rv"], C.c_uint64), _ptr(cols["ns_id"], C.c_uint32),
+                                      _ptr(cols["phase"], C.c_uint8), _ptr(cols["type"], C.c_uint8))
+    _abi.check(rc)
+    return cols
+
+
+def shard_of(uid_hi: int, uid_lo: int, n_shards: int) -> int:
+    return int(_abi.lib().pte_shard_of(int(uid_hi), int(uid_lo), int(n_shards)))
+
+
+class PinnedBuffer:
+    """Page-locked host array (pte_host_alloc) viewed through numpy."""
+
+    def __init__(self, count: int, dtype):
+        self.dtype = np.dtype(dtype)
+        self.nbytes = max(1, count * self.dtype.itemsize)
+        self._ptr = _abi.lib().pte_host_alloc(self.nbytes)
+        if not self._ptr:
+            raise MemoryError("pte_host_alloc(%d) failed: %s" % (self.nbytes, _abi.last_error(None)))
+        buf = (C.c_uint8 * self.nbytes).from_address(self._ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=count)
+
+    def free(self):
+        if self._ptr:
+            self.array = None
+            _abi.lib().pte_host_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+@dataclass
+class EmittedColumns:
+    """Emitted records in replay order (what the sink is handed)."""
+    idx: np.ndarray      # arrival index in the ingested log
+    rv: np.ndarray
+    key: np.ndarray      # interned 64-bit uid key
+    ns_id: np.ndarray
+    phase: np.ndarray
+    type: np.ndarray
+
+    def __len__(self):
+        return int(self.idx.shape[0])
+
+
+class PhaseTransitionEngine:
+    """One engine handle, bound to one GPU.  Not thread-safe."""
+
+    def __init__(self, max_events: int, max_pods: int = 0, device: int = 0):
+        L = _abi.lib()
+        if _abi.device_count() <= 0:
+            raise PteError(-3, "no CUDA device: the phase-transition engine has no CPU path")
+        self._h = C.c_void_p()
+        _abi.check(L.pte_create(int(device), int(max_events), int(max_pods), C.byref(self._h)))
+        self._L = L
+        self.max_events, self.device = int(max_events), int(device)
+        self.last_stats: Optional[Dict[str, float]] = None
+
+    # -- lifetime
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pte_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int):
+        _abi.check(rc, self._h)
+
+    # -- configuration
+    def set_filters(self, ns_allow: Optional[Iterable[int]] = None, *, ns_filter_on: bool = False,
+                    critical_only: bool = False):
+        ids = np.ascontiguousarray(sorted(set(int(x) for x in ns_allow)) if ns_allow else [], dtype=np.uint32)
+        self._ck(self._L.pte_set_filters(self._h, _ptr(ids, C.c_uint32) if ids.size else None, int(ids.size),
+                                         int(bool(ns_filter_on)), int(bool(critical_only))))
+
+    # -- input
+    def ingest(self, cols: Dict[str, np.ndarray]):
+        n = int(cols["rv"].shape[0])
+        c = {name: np.ascontiguousarray(cols[name], dtype=dt) for name, dt in COLUMNS}
+        for name, _ in COLUMNS:
+            if c[name].shape[0] != n:
+                raise ValueError("column %s has %d rows, rv has %d" % (name, c[name].shape[0], n))
+        self._ck(self._L.pte_ingest(self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64),
+                                    _ptr(c["rv"], C.c_uint64), _ptr(c["ns_id"], C.c_uint32),
+                                    _ptr(c["phase"], C.c_uint8), _ptr(c["type"], C.c_uint8), n))
+
+    def generate(self, seed: int, n_events: int, n_pods: int, **kw):
+        p = gen_params(seed, n_events, n_pods, **kw)
+        self._ck(self._L.pte_generate(self._h, C.byref(p)))
+
+    def read_log(self, into: Optional[Dict[str, np.ndarray]] = None) -> Dict[str, np.ndarray]:
+        n = C.c_uint64()
+        self._ck(self._L.pte_read_log(self._h, None, None, None, None, None, None, 1 << 62, C.byref(n)))
+        cols = into or {name: np.empty(n.value, dt) for name, dt in COLUMNS}
+        self._ck(self._L.pte_read_log(self._h, _ptr(cols["uid_hi"], C.c_uint64), _ptr(cols["uid_lo"], C.c_uint64),
+                                      _ptr(cols["rv"], C.c_uint64), _ptr(cols["ns_id"], C.c_uint32),
+                                      _ptr(cols["phase"], C.c_uint8), _ptr(cols["type"], C.c_uint8),
+                                      int(cols["rv"].shape[0]), C.byref(n)))
+        return cols
+
+    # -- the hot path
+    def run(self, dedupe: bool = True) -> Dict[str, float]:
+        st = PteStats()
+        self._ck(self._L.pte_run(self._h, int(bool(dedupe)), C.byref(st)))
+        self.last_stats = st.as_dict()
+        return self.last_stats
+
+    def fetch(self, columns: Sequence[str] = ("idx", "rv", "key", "ns_id", "phase", "type"),
+              into: Optional[Dict[str, np.ndarray]] = None) -> EmittedColumns:
+        n = int(self.last_stats["n_emitted"]) if self.last_stats else 0
+        dts = dict(idx=np.uint32, rv=np.uint64, key=np.uint64, ns_id=np.uint32, phase=np.uint8, type=np.uint8)
+        out = {}
+        for name in dts:
+            if into is not None and name in into:
+                out[name] = into[name]
+            elif name in columns:
+                out[name] = np.empty(n, dts[name])
+            else:
+                out[name] = None
+        cap = min(int(a.shape[0]) for a in out.values() if a is not None) if any(a is not None for a in out.values()) else n
+        got = C.c_uint64()
+        self._ck(self._L.pte_fetch(self._h, _ptr(out["idx"], C.c_uint32), _ptr(out["rv"], C.c_uint64),
+                                   _ptr(out["key"], C.c_uint64), _ptr(out["ns_id"], C.c_uint32),
+                                   _ptr(out["phase"], C.c_uint8), _ptr(out["type"], C.c_uint8), cap, C.byref(got)))
+        k = int(got.value)
+        z = {name: (np.empty(0, dts[name]) if a is None else a[:k]) for name, a in out.items()}
+        return EmittedColumns(**z)
+
+    def digest(self) -> int:
+        d = C.c_uint64()
+        self._ck(self._L.pte_digest(self._h, C.byref(d)))
+        return int(d.value)
+
+    def debug_sort(self, records: np.ndarray, bit_lo: int, bit_hi: int) -> np.ndarray:
+        r = np.ascontiguousarray(records, dtype=np.uint64).copy()
+        self._ck(self._L.pte_debug_sort_u64(self._h, _ptr(r, C.c_uint64), int(r.shape[0]), bit_lo, bit_hi))
+        return r
+
+    # -- multi-GPU
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        _abi.check(_abi.lib().pte_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, n_ranks: int):
+        assert len(unique_id) == 128
+        self.n_ranks = n_ranks
+        self._ck(self._L.pte_comm_init(self._h, unique_id, rank, n_ranks))
+
+    def gather_counts(self) -> np.ndarray:
+        n = getattr(self, "n_ranks", 1)
+        out = np.zeros(4 * n, np.uint64)
+        self._ck(self._L.pte_gather_counts(self._h, _ptr(out, C.c_uint64)))
+        return out.reshape(n, 4)

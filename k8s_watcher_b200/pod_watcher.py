@@ -1,0 +1,267 @@
+"""Drop-in for the reference's ``watcher.pod_watcher.PodWatcher`` whose event path runs in bulk on a B200.
+
+Same class surface as the reference (watcher/pod_watcher.py:10-277): ``PodWatcher(environment)``
+with ``.environment .config .v1 .watch .logger``, ``setup_k8s_client()``,
+``should_process_event()``, ``handle_pod_event()``, ``_extract_pod_data()``, ``start_watching()``,
+and the same error conventions (set-up failure -> False + error log, stream failure -> log and
+re-raise, ``watch.stop()`` always).  What changes is where the work happens:
+
+* ``handle_pod_event`` does not decide anything itself; it queues the event.
+* ``flush()`` / ``replay(log)`` hand the whole batch to the CUDA engine (libpte.so), which applies
+  the reference's two filters, and -- with ``dedupe=True`` -- the last-known-phase layer the
+  reference's README promises but pod_watcher.py never implemented.
+  ``dedupe=False`` reproduces the reference literally: every event that reaches the POST site.
+* emitted records come back as a :class:`Batch`; the sink takes it in one call.
+
+There is no CPU implementation of the path in this package: without libpte.so and a CUDA
+device ``replay``/``flush`` raise.
+"""
+from __future__ import annotations
+
+import logging
+import os
+from datetime import datetime
+from typing import Any, Dict, Iterator, List, Optional
+
+import yaml
+
+try:                                     # a real kubernetes install wins
+    from kubernetes import client, config, watch
+    from kubernetes.config import ConfigException
+except ImportError:                      # this image: no package, no network
+    from ._k8s_stub import client, config, watch, ConfigException
+
+from . import codes
+from .clusterapi_client import ClusterApiClient
+from .engine import EmittedColumns, PhaseTransitionEngine
+from .replay_log import ReplayLog
+
+
+class Batch:
+    """Emitted notifications of one replay, in replay order."""
+
+    def __init__(self, watcher: "PodWatcher", log: ReplayLog, emitted: EmittedColumns, stats: Dict[str, float],
+                 dedupe: bool):
+        self.watcher, self.log, self.emitted, self.stats, self.dedupe = watcher, log, emitted, stats, dedupe
+
+    def __len__(self):
+        return len(self.emitted)
+
+    @property
+    def indices(self):
+        """Arrival indices (into the log) of the emitted events."""
+        return self.emitted.idx
+
+    def payloads(self, event_timestamp: Optional[str] = None) -> Iterator[Dict[str, Any]]:
+        """Payload dicts exactly as the reference builds them at pod_watcher.py:232-233,
+        one per emitted record.  ``event_timestamp`` pins the wall-clock field (:199)."""
+        for i, t in zip(self.emitted.idx.tolist(), self.emitted.type.tolist()):
+            d = self.watcher._extract_pod_data(self.log.pod_at(i), event_timestamp=event_timestamp)
+            d["event_type"] = codes.TYPE_NAMES[t]
+            yield d
+
+
+class PodWatcher:
+    def __init__(self, environment: str = "development", *, dedupe: bool = True,
+                 sink: Optional[ClusterApiClient] = None, engine: Optional[PhaseTransitionEngine] = None,
+                 device: int = 0, config_dir: str = "config"):
+        self.environment = environment
+        self.config_dir = config_dir           # CWD-relative by default, like upstream (:22,:25)
+        self.config = self._load_environment_config()
+        self.v1 = None
+        self.watch = watch.Watch()
+        self._setup_logging()
+        self.dedupe = dedupe
+        self.clusterapi_client = sink          # the reference leaves this commented out (:14)
+        self._engine = engine
+        self._device = device
+        self._pending: List[Dict[str, Any]] = []
+        self.batches: List[Batch] = []
+
+    # ---- configuration (pod_watcher.py:19-75) ---------------------------------
+    def _load_environment_config(self) -> Dict[str, Any]:
+        base = self._load_config_file("%s/base.yaml" % self.config_dir)
+        env = self._load_config_file("%s/%s.yaml" % (self.config_dir, self.environment))
+        return self._substitute_env_vars(self._merge_configs(base, env))
+
+    def _load_config_file(self, config_file: str) -> Dict[str, Any]:
+        def say(msg, level):
+            if hasattr(self, "logger"):
+                getattr(self.logger, level)(msg)
+            else:
+                print(msg)
+        try:
+            with open(config_file, "r") as fh:
+                return yaml.safe_load(fh) or {}
+        except FileNotFoundError:
+            say("Config file %s not found" % config_file, "warning")
+            return {}
+        except Exception as e:
+            say("Error loading config %s: %s" % (config_file, e), "error")
+            return {}
+
+    def _merge_configs(self, base: Dict[str, Any], override: Dict[str, Any]) -> Dict[str, Any]:
+        merged = dict(base)
+        for key, value in override.items():
+            if isinstance(merged.get(key), dict) and isinstance(value, dict):
+                merged[key] = self._merge_configs(merged[key], value)
+            else:
+                merged[key] = value
+        return merged
+
+    def _substitute_env_vars(self, cfg: Dict[str, Any]) -> Dict[str, Any]:
+        def walk(node):
+            if isinstance(node, dict):
+                return {k: walk(v) for k, v in node.items()}
+            if isinstance(node, list):
+                return [walk(v) for v in node]
+            if isinstance(node, str) and node.startswith("${") and node.endswith("}"):
+                name, default = node[2:-1], ""
+                if ":-" in name:
+                    name, default = name.split(":-", 1)
+                return os.getenv(name, default)
+            return node
+        return walk(cfg)
+
+    def _setup_logging(self):
+        level = getattr(logging, self.config.get("watcher", {}).get("log_level", "INFO"))
+        if self.environment == "production":          # JSON-shaped lines in production (:82-84)
+            fmt = ('{"timestamp":"%(asctime)s","level":"%(levelname)s","logger":"%(name)s",'
+                   '"message":"%(message)s","environment":"' + self.environment + '"}')
+        else:
+            fmt = "[%s] %%(asctime)s - %%(name)s - %%(levelname)s - %%(message)s" % self.environment.upper()
+        logging.basicConfig(level=level, format=fmt)
+        self.logger = logging.getLogger(__name__)
+        self.logger.info("Starting k8s-watcher in %s environment", self.environment)
+
+    # ---- kubernetes client (pod_watcher.py:110-157) -----------------------------
+    def setup_k8s_client(self) -> bool:
+        try:
+            k8s = self.config.get("kubernetes", {})
+            if k8s.get("use_incluster_config", False):
+                self.logger.info("Using in-cluster configuration")
+                config.load_incluster_config()
+            elif "config_file" in k8s:
+                path = k8s["config_file"]
+                self.logger.info("Loading kubeconfig from: %s", path)
+                if not os.path.exists(path):
+                    self.logger.error("Kubeconfig file not found: %s", path)
+                    return False
+                config.load_kube_config(config_file=path)
+            else:
+                self.logger.info("Using default kubeconfig")
+                config.load_kube_config()
+            self.v1 = client.CoreV1Api()
+            self.logger.info("Successfully connected to Kubernetes API version: %s", self.v1.get_api_version())
+            if self.environment != "local":
+                sample = [ns.metadata.name for ns in self.v1.list_namespace().items[:5]]
+                self.logger.info("Sample namespaces: %s", sample)
+            return True
+        except ConfigException as e:
+            self.logger.error("Kubernetes config error: %s", e)
+            return False
+        except Exception as e:
+            self.logger.error("Error setting up k8s client: %s", e)
+            return False
+
+    # ---- per-event surface, kept for callers and for payload materialisation -----
+    def _extract_pod_data(self, pod, event_timestamp: Optional[str] = None) -> Dict[str, Any]:
+        """Payload for one pod; same keys, order and defaults as pod_watcher.py:159-202."""
+        md, st, sp = pod.metadata, pod.status, pod.spec
+        conditions, container_statuses, containers = [], [], []
+        if st:
+            for c in (st.conditions or []):
+                conditions.append({"type": c.type, "status": c.status, "reason": c.reason, "message": c.message})
+            for cs in (st.container_statuses or []):
+                container_statuses.append({"name": cs.name, "ready": cs.ready, "restart_count": cs.restart_count,
+                                           "state": str(cs.state) if cs.state else None})
+        if sp:
+            for c in (sp.containers or []):
+                containers.append({"name": c.name, "image": c.image})
+        created = md.creation_timestamp
+        return {
+            "name": md.name,
+            "namespace": md.namespace,
+            "uid": md.uid,
+            "environment": self.environment,
+            "status": {"phase": st.phase if st else "Unknown", "conditions": conditions,
+                       "container_statuses": container_statuses},
+            "spec": {"node_name": sp.node_name if sp else None, "containers": containers},
+            "metadata": {"labels": md.labels or {}, "annotations": md.annotations or {},
+                         "creation_timestamp": created.isoformat() if created else None},
+            "event_timestamp": event_timestamp if event_timestamp is not None else datetime.now().isoformat(),
+        }
+
+    def _critical_only(self) -> bool:
+        return self.environment == "production" and bool(
+            self.config.get("watcher", {}).get("alerts", {}).get("critical_events_only", False))
+
+    def should_process_event(self, event_type: str, pod) -> bool:
+        """Host form of the first device predicate (pod_watcher.py:204-212)."""
+        if self._critical_only() and event_type not in ["DELETED"] and pod.status \
+                and pod.status.phase not in ["Failed", "Succeeded"]:
+            return False
+        return True
+
+    def handle_pod_event(self, event_type: str, pod) -> None:
+        """Queue one event for the next bulk replay (the reference decides per event, :214-241)."""
+        self._pending.append({"type": event_type, "object": pod})
+
+    # ---- bulk path -----------------------------------------------------------------
+    def _engine_for(self, n_events: int, n_pods_hint: int) -> PhaseTransitionEngine:
+        eng = self._engine
+        if eng is None or eng.max_events < n_events:
+            if eng is not None:
+                eng.close()
+            eng = self._engine = PhaseTransitionEngine(max(n_events, 1024), max(n_pods_hint, 0), device=self._device)
+        return eng
+
+    def replay(self, log: ReplayLog, *, dedupe: Optional[bool] = None, max_pods: int = 0) -> Batch:
+        """Run a whole log through the engine and return what a watcher would have notified."""
+        dedupe = self.dedupe if dedupe is None else dedupe
+        eng = self._engine_for(len(log), max_pods)
+        names = self.config.get("watcher", {}).get("namespaces", []) or []
+        eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
+        eng.ingest(log.columns)
+        stats = eng.run(dedupe=dedupe)
+        batch = Batch(self, log, eng.fetch(), stats, dedupe)
+        self.batches.append(batch)
+        return batch
+
+    def flush(self) -> Optional[Batch]:
+        """Replay everything queued by handle_pod_event; hand the result to the sink if there is one."""
+        if not self._pending:
+            return None
+        log = ReplayLog.from_events(self._pending)
+        self._pending = []
+        batch = self.replay(log)
+        if self.clusterapi_client is not None:
+            sent = self.clusterapi_client.update_pod_status_batch(batch)
+            if sent != len(batch):
+                self.logger.error("Failed to notify clusterapi about %d of %d events", len(batch) - sent, len(batch))
+        return batch
+
+    def start_watching(self):
+        """Live loop (pod_watcher.py:243-277): same set-up, same error handling; events are queued
+        and replayed in bulk when the stream ends or the watcher is interrupted."""
+        if not self.setup_k8s_client():
+            self.logger.error("Failed to setup Kubernetes client")
+            return
+        self.logger.info("Starting Pod watcher in %s environment...", self.environment)
+        targets = self.config.get("watcher", {}).get("namespaces", [])
+        if targets:
+            self.logger.info("Monitoring namespaces: %s", targets)
+        else:
+            self.logger.info("Monitoring all namespaces")
+        try:
+            for event in self.watch.stream(self.v1.list_pod_for_all_namespaces):
+                self.handle_pod_event(event["type"], event["object"])
+            self.flush()
+        except KeyboardInterrupt:
+            self.logger.info("Stopping Pod watcher...")
+            self.flush()
+        except Exception as e:
+            self.logger.error("Error in Pod watcher: %s", e)
+            raise
+        finally:
+            self.watch.stop()

@@ -1,0 +1,119 @@
+"""Replay logs: pod-watch events as integer columns plus the dictionaries to get back.
+
+A log row is what the reference reads from one watch event (watcher/pod_watcher.py:162-167,
+:216-217, :267-268) plus ``metadata.resource_version`` as the order key.
+"""
+from __future__ import annotations
+
+import datetime as _dt
+from typing import Any, Dict, Iterable, List, Optional
+
+import numpy as np
+
+from . import codes
+from .engine import COLUMNS, generate_host
+
+
+class _Attr:
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+
+class ReplayLog:
+    def __init__(self, columns: Dict[str, np.ndarray], namespaces: List[str], phases: Optional[List[Any]] = None,
+                 pods: Optional[List[Any]] = None):
+        self.columns = {name: np.ascontiguousarray(columns[name], dtype=dt) for name, dt in COLUMNS}
+        self.namespaces = list(namespaces)
+        # code -> phase string; codes 0..6 are fixed by include/pte.h
+        self.phases = list(phases) if phases else list(codes.PHASE_NAMES) + [None, None]
+        self._pods = pods            # per-row pod objects when the log came from a live stream
+
+    def __len__(self):
+        return int(self.columns["rv"].shape[0])
+
+    # ---- construction -------------------------------------------------------
+    @classmethod
+    def from_events(cls, events: Iterable[Dict[str, Any]]) -> "ReplayLog":
+        """Intern a stream of ``{'type': str, 'object': V1Pod}`` dicts (pod_watcher.py:267-268)."""
+        events = list(events)
+        n = len(events)
+        cols = {name: np.zeros(n, dt) for name, dt in COLUMNS}
+        ns_ids: Dict[str, int] = {}
+        phase_ids: Dict[Any, int] = {p: i for i, p in enumerate(codes.PHASE_NAMES)}
+        phases: List[Any] = list(codes.PHASE_NAMES) + [None, None]
+        pods = []
+        for i, ev in enumerate(events):
+            t = ev["type"]
+            pod = ev["object"]
+            if t not in codes.TYPE_CODE:
+                raise ValueError("event %d: type %r is not ADDED/MODIFIED/DELETED" % (i, t))
+            md = pod.metadata
+            hi, lo = codes.str_to_uid(md.uid)
+            cols["uid_hi"][i], cols["uid_lo"][i] = hi, lo
+            rvs = getattr(md, "resource_version", None)
+            cols["rv"][i] = int(rvs) if rvs not in (None, "") else i + 1
+            cols["ns_id"][i] = ns_ids.setdefault(md.namespace, len(ns_ids))
+            st = pod.status
+            if not st:
+                code = codes.PH_NOSTATUS
+            elif st.phase is None:
+                code = codes.PH_NULL
+            else:
+                code = phase_ids.get(st.phase)
+                if code is None:
+                    code = len(phases)
+                    if code > codes.PH_MAX:
+                        raise ValueError("more than %d distinct phase strings" % (codes.PH_MAX - 6))
+                    phase_ids[st.phase] = code
+                    phases.append(st.phase)
+            cols["phase"][i] = code
+            cols["type"][i] = codes.TYPE_CODE[t]
+            pods.append(pod)
+        names = [None] * len(ns_ids)
+        for k, v in ns_ids.items():
+            names[v] = k
+        return cls(cols, names, phases, pods)
+
+    @classmethod
+    def synthetic(cls, seed: int, n_events: int, n_pods: int, **kw) -> "ReplayLog":
+        """The synthetic log of include/pte.h (host generator of libpte.so)."""
+        return cls(generate_host(seed, n_events, n_pods, **kw), list(codes.DEFAULT_NAMESPACES))
+
+    # ---- the way back ---------------------------------------------------------
+    def namespace_ids(self, names: Iterable[str]) -> List[int]:
+        """ids of those allow-list names that occur in this log (others can never match)."""
+        lut = {n: i for i, n in enumerate(self.namespaces)}
+        return [lut[n] for n in names if n in lut]
+
+    def pod_at(self, i: int):
+        """Pod object of row i: the original one for stream logs, a minimal one for column logs."""
+        if self._pods is not None:
+            return self._pods[i]
+        c = self.columns
+        code = int(c["phase"][i])
+        uid = codes.uid_to_str(c["uid_hi"][i], c["uid_lo"][i])
+        md = _Attr(name="pod-" + uid[:13], namespace=self.namespaces[int(c["ns_id"][i])], uid=uid, labels=None,
+                   annotations=None, creation_timestamp=None, resource_version=str(int(c["rv"][i])))
+        status = None if code == codes.PH_NOSTATUS else _Attr(phase=self.phases[code], conditions=None,
+                                                              container_statuses=None)
+        return _Attr(metadata=md, status=status, spec=None)
+
+    def type_at(self, i: int) -> str:
+        return codes.TYPE_NAMES[int(self.columns["type"][i])]
+
+    def events(self):
+        for i in range(len(self)):
+            yield {"type": self.type_at(i), "object": self.pod_at(i)}
+
+    def shard(self, n_shards: int) -> List["ReplayLog"]:
+        """Split by uid hash (pte_shard_of), keeping arrival order inside every shard."""
+        from .engine import shard_of
+        hi = self.columns["uid_hi"]
+        lo = self.columns["uid_lo"]
+        owner = np.fromiter((shard_of(int(h), int(l), n_shards) for h, l in zip(hi, lo)), np.int64, len(self))
+        out = []
+        for g in range(n_shards):
+            sel = np.nonzero(owner == g)[0]
+            pods = [self._pods[i] for i in sel] if self._pods is not None else None
+            out.append(ReplayLog({k: v[sel] for k, v in self.columns.items()}, self.namespaces, self.phases, pods))
+        return out

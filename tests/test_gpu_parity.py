@@ -1,0 +1,317 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle.  Needs a B200: -m gpu."""
+import glob
+import gzip
+import json
+import os
+
+import numpy as np
+import pytest
+
+import fake_kubernetes as fk
+from k8s_watcher_b200 import PhaseTransitionEngine, PodWatcher, PteError, ReplayLog, generate_host
+from oracle import c_oracle
+from oracle import podwatch_oracle as po
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "ref_*.json.gz")))
+SEED = 0x6B38735F77617463
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = PhaseTransitionEngine(4_000_000, 300_000)
+    yield e
+    e.close()
+
+
+# ---- the sort in isolation ---------------------------------------------------
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 32, 33, 255, 4095, 4096, 4097, 8191, 65_537, 1_000_003, 3_999_999])
+def test_radix_sort_matches_numpy_stable(eng, n):
+    rng = np.random.default_rng(n + 1)
+    rec = rng.integers(0, 1 << 63, n, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, n, dtype=np.uint64)
+    for lo, hi in ((0, 64), (8, 38), (38, 62), (5, 6), (17, 17), (40, 47)):
+        got = eng.debug_sort(rec, lo, hi)
+        field = (rec >> np.uint64(lo)) & np.uint64((1 << (hi - lo)) - 1) if hi > lo else np.zeros(n, np.uint64)
+        want = rec[np.argsort(field, kind="stable")]
+        assert np.array_equal(got, want), (n, lo, hi)
+
+
+@pytest.mark.parametrize("kind", ["constant", "two_values", "sorted", "reversed", "hot_bin"])
+def test_radix_sort_skewed_inputs(eng, kind):
+    n = 700_001
+    rng = np.random.default_rng(5)
+    low = rng.integers(0, 1 << 20, n, dtype=np.uint64)      # payload bits that must keep their order
+    if kind == "constant":
+        key = np.full(n, 77, np.uint64)
+    elif kind == "two_values":
+        key = rng.integers(0, 2, n, dtype=np.uint64) * np.uint64(0xABCDEF)
+    elif kind == "sorted":
+        key = np.arange(n, dtype=np.uint64)
+    elif kind == "reversed":
+        key = np.arange(n, dtype=np.uint64)[::-1].copy()
+    else:
+        key = np.where(rng.random(n) < 0.9, np.uint64(0x1234), rng.integers(0, 1 << 24, n, dtype=np.uint64))
+    rec = (key << np.uint64(20)) | low
+    got = eng.debug_sort(rec, 20, 44)
+    want = rec[np.argsort(key, kind="stable")]
+    assert np.array_equal(got, want)
+
+
+# ---- the generator -----------------------------------------------------------
+@pytest.mark.parametrize("kw", [
+    dict(n=1000, pods=50, dist=0, p_del=0.05),
+    dict(n=300_000, pods=7_000, dist=0, p_del=0.0),
+    dict(n=300_000, pods=7_000, dist=1, p_del=0.05, p_nostatus=0.02, p_null=0.02),
+    dict(n=100_000, pods=1, dist=1, p_del=0.3),
+    dict(n=50_000, pods=9_000, dist=0, p_del=0.05, shard=3, n_shards=8),
+])
+def test_device_generator_matches_host_and_oracle(eng, kw):
+    kw = dict(kw)
+    n, pods = kw.pop("n"), kw.pop("pods")
+    eng.generate(SEED, n, pods, **kw)
+    dev = eng.read_log()
+    host = generate_host(SEED, n, pods, **kw)
+    orc = c_oracle.generate(SEED, n, pods, **kw)
+    for k in orc:
+        assert np.array_equal(host[k], orc[k]), ("host", k)
+        assert np.array_equal(dev[k], orc[k]), ("device", k)
+
+
+# ---- replay parity ------------------------------------------------------------
+FILTERS = {
+    "staging": dict(critical_only=False, ns_allow=None),
+    "development": dict(critical_only=False, ns_allow=[0, 1]),
+    "production": dict(critical_only=True, ns_allow=[0, 1, 2, 3]),
+}
+
+
+def run_engine(eng, cols, flt, dedupe):
+    eng.set_filters(flt["ns_allow"], critical_only=flt["critical_only"])
+    eng.ingest(cols)
+    st = eng.run(dedupe=dedupe)
+    return eng.fetch(), st
+
+
+def check_against_oracle(eng, cols, flt, dedupe, pods):
+    got, st = run_engine(eng, cols, flt, dedupe)
+    idx, ost, dig = c_oracle.replay(cols, critical_only=flt["critical_only"], ns_allow=flt["ns_allow"], dedupe=dedupe,
+                                    pods_hint=pods)
+    assert {k: st[k] for k in ost} == ost
+    assert np.array_equal(got.idx.astype(np.uint64), idx)
+    i = idx.astype(np.int64)
+    assert np.array_equal(got.rv, cols["rv"][i])
+    assert np.array_equal(got.ns_id, cols["ns_id"][i])
+    assert np.array_equal(got.phase, cols["phase"][i])
+    assert np.array_equal(got.type, cols["type"][i])
+    # the interned key is a bijection of the uid
+    if len(i):
+        uid = cols["uid_hi"][i].astype(object) * (1 << 64) + cols["uid_lo"][i].astype(object)
+        pairs = set(zip(uid.tolist(), got.key.tolist()))
+        assert len(pairs) == len(set(uid.tolist())) == len(set(got.key.tolist()))
+    assert eng.digest() == dig
+    return st
+
+
+@pytest.mark.parametrize("env", list(FILTERS))
+@pytest.mark.parametrize("dedupe", [True, False])
+@pytest.mark.parametrize("shape", [
+    dict(n=1000, pods=50, dist=0, p_del=0.05),                              # BASELINE config 1
+    dict(n=250_000, pods=4_000, dist=0, p_del=0.0),
+    dict(n=250_000, pods=4_000, dist=1, p_del=0.05, p_nostatus=0.03, p_null=0.03),
+])
+def test_replay_matches_oracle(eng, env, dedupe, shape):
+    shape = dict(shape)
+    n, pods = shape.pop("n"), shape.pop("pods")
+    cols = c_oracle.generate(SEED + 1, n, pods, **shape)
+    check_against_oracle(eng, cols, FILTERS[env], dedupe, pods)
+
+
+@pytest.mark.parametrize("n,pods", [(1, 1), (2, 1), (3, 2), (1023, 5), (1024, 5), (1025, 5), (4097, 4097)])
+def test_ragged_sizes(eng, n, pods):
+    cols = c_oracle.generate(n * 31 + pods, n, pods, dist=n % 2, p_del=0.2, p_nostatus=0.1, p_null=0.1)
+    for env in FILTERS:
+        check_against_oracle(eng, cols, FILTERS[env], True, pods)
+
+
+def test_empty_log(eng):
+    cols = c_oracle.generate(1, 0, 10)
+    got, st = run_engine(eng, cols, FILTERS["staging"], True)
+    assert len(got) == 0 and st["n_emitted"] == 0 and eng.digest() == 0
+
+
+def test_everything_filtered_out(eng):
+    cols = c_oracle.generate(2, 5000, 100)
+    eng.set_filters([], ns_filter_on=True)          # allow-list names that never occur in the log
+    eng.ingest(cols)
+    st = eng.run()
+    assert st["n_survived"] == 0 and st["n_emitted"] == 0 and len(eng.fetch()) == 0
+
+
+def test_single_pod_all_same_phase(eng):
+    n = 100_000
+    cols = c_oracle.generate(3, n, 1)
+    cols["phase"][:] = po.PH_RUNNING
+    got, st = run_engine(eng, cols, FILTERS["staging"], True)
+    assert st["n_emitted"] == 1 and got.idx.tolist() == [0]
+
+
+def test_all_deleted_are_tombstones(eng):
+    n = 50_000
+    cols = c_oracle.generate(4, n, 300)
+    cols["type"][:] = po.TYPE_DELETED
+    got, st = run_engine(eng, cols, FILTERS["production"], True)
+    keep = np.isin(cols["ns_id"], [0, 1, 2, 3])
+    assert st["n_emitted"] == st["n_tombstones"] == int(keep.sum())
+    assert np.array_equal(got.idx, np.nonzero(keep)[0].astype(np.uint32))
+
+
+def test_statusless_and_unknown_share_an_effective_phase(eng):
+    # NOSTATUS then Unknown for the same pod: the payload says "Unknown" twice -> one notification
+    cols = c_oracle.generate(5, 4, 1)
+    cols["type"][:] = [0, 1, 1, 1]
+    cols["phase"][:] = [po.PH_NOSTATUS, po.PH_UNKNOWN, po.PH_NOSTATUS, po.PH_RUNNING]
+    got, st = run_engine(eng, cols, FILTERS["staging"], True)
+    assert got.idx.tolist() == [0, 3]
+
+
+def test_dictionary_is_exact_for_adversarial_uids(eng):
+    # uids that differ in one half only, and uids with a zero half
+    n = 60_000
+    rng = np.random.default_rng(11)
+    base = rng.integers(1, 1 << 62, 200, dtype=np.uint64)
+    pick = rng.integers(0, 200, n)
+    cols = c_oracle.generate(6, n, 200)
+    cols["uid_hi"][:] = np.where(pick % 3 == 0, np.uint64(0), base[pick])
+    cols["uid_lo"][:] = np.where(pick % 3 == 1, np.uint64(0), base[(pick * 7) % 200])
+    cols["uid_lo"][(cols["uid_hi"] == 0) & (cols["uid_lo"] == 0)] = 9
+    check_against_oracle(eng, cols, FILTERS["staging"], True, 1000)
+
+
+def test_config2_full_parity():
+    """BASELINE config 2: 10 M events / 100 k pods, uniform churn -- every emitted record compared."""
+    n, pods = 10_000_000, 100_000
+    with PhaseTransitionEngine(n, pods) as e:
+        e.generate(SEED, n, pods)
+        st = e.run()
+        got = e.fetch(columns=("idx", "type", "phase"))
+        cols = c_oracle.generate(SEED, n, pods)
+        idx, ost, dig = c_oracle.replay(cols, pods_hint=pods)
+        assert np.array_equal(got.idx.astype(np.uint64), idx)
+        assert {k: st[k] for k in ost} == ost and e.digest() == dig
+        assert 0.79 < st["n_emitted"] / n < 0.82          # f = h + (1-h) * 0.8
+
+
+def test_zipf_with_tombstones_digest_100m():
+    """Shape of BASELINE config 4 at 100 M events: octave-Zipf pod activity, 5 % delete draws.
+    Too big to compare record by record here, so counts + order-sensitive digest."""
+    n, pods = 100_000_000, 1_000_000
+    with PhaseTransitionEngine(n, pods) as e:
+        e.generate(SEED, n, pods, dist=1, p_del=0.05)
+        st = e.run()
+        ost, dig = c_oracle.generate_replay(SEED, n, pods, dist=1, p_del=0.05)
+        assert {k: st[k] for k in ost} == ost
+        assert e.digest() == dig
+        # idempotence: the same log replays to the same answer
+        st2 = e.run()
+        assert st2["n_emitted"] == st["n_emitted"] and e.digest() == dig
+
+
+# ---- errors are loud -------------------------------------------------------------
+def test_bad_event_is_rejected(eng):
+    cols = c_oracle.generate(7, 1000, 10)
+    cols["type"][500] = 3          # an ERROR/BOOKMARK event: the reference would crash at pod_watcher.py:216
+    eng.set_filters(None)
+    eng.ingest(cols)
+    with pytest.raises(PteError) as ei:
+        eng.run()
+    assert ei.value.code == -6
+
+
+def test_zero_uid_is_rejected(eng):
+    cols = c_oracle.generate(8, 1000, 10)
+    cols["uid_hi"][3] = 0
+    cols["uid_lo"][3] = 0
+    eng.ingest(cols)
+    with pytest.raises(PteError) as ei:
+        eng.run()
+    assert ei.value.code == -6
+
+
+def test_unordered_log_is_rejected(eng):
+    cols = c_oracle.generate(9, 5000, 10)
+    cols["rv"][[100, 4000]] = cols["rv"][[4000, 100]]
+    eng.ingest(cols)
+    with pytest.raises(PteError) as ei:
+        eng.run()
+    assert ei.value.code == -7
+
+
+def test_too_many_pods_is_rejected():
+    with PhaseTransitionEngine(100_000, 64) as e:     # table sized for 64 uids
+        e.ingest(c_oracle.generate(10, 100_000, 50_000))
+        with pytest.raises(PteError) as ei:
+            e.run()
+        assert ei.value.code == -5
+
+
+def test_capacity_errors(eng):
+    with pytest.raises(PteError):
+        eng.ingest(c_oracle.generate(1, 4_000_001, 10))
+    with pytest.raises(PteError):
+        PhaseTransitionEngine(1 << 30, 10)
+    fresh = PhaseTransitionEngine(1000, 10)
+    with pytest.raises(PteError):
+        fresh.fetch()
+    fresh.close()
+
+
+# ---- through the reference-shaped surface, against what the real reference produced ------
+def _load(path):
+    with gzip.open(path, "rb") as f:
+        fx = json.loads(f.read())
+    dt = dict(uid_hi=np.uint64, uid_lo=np.uint64, rv=np.uint64, ns_id=np.uint32, phase=np.uint8, type=np.uint8)
+    fx["cols"] = {k: np.array(v, dtype=dt[k]) for k, v in fx["columns"].items()}
+    return fx
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[4:-8] for p in GOLDEN])
+def test_podwatcher_replay_matches_reference_payloads(path, monkeypatch):
+    fx = _load(path)
+    monkeypatch.chdir(ROOT)
+    w = PodWatcher(fx["env"])
+    assert w.config == fx["config"]
+    log = ReplayLog.from_events(fk.events_from_columns(fx["cols"]))
+    # R-trace: byte-identical wire bodies to the real reference's payloads
+    batch = w.replay(log, dedupe=False)
+    assert batch.indices.tolist() == fx["r_trace"]
+    got = list(batch.payloads(event_timestamp=fx["frozen_timestamp"]))
+    assert got == fx["payloads"]
+    assert [json.dumps(d, allow_nan=False) for d in got] == [json.dumps(d, allow_nan=False) for d in fx["payloads"]]
+    # T-trace: the transition layer applied to the real reference's payloads
+    keep = po.transition_filter(fx["payloads"])
+    tb = w.replay(log, dedupe=True)
+    assert tb.indices.tolist() == [fx["r_trace"][k] for k in keep]
+    assert list(tb.payloads(event_timestamp=fx["frozen_timestamp"])) == [fx["payloads"][k] for k in keep]
+
+
+def test_live_loop_surface_with_mock_sink(monkeypatch):
+    """start_watching() over a replayed stream (BASELINE config 1 shape) ends with the sink holding
+    exactly the transition payloads, in order."""
+    from k8s_watcher_b200 import ClusterApiClient, _k8s_stub
+    fx = _load([p for p in GOLDEN if "c1_staging" in p][0])
+    monkeypatch.chdir(ROOT)
+    events = fk.events_from_columns(fx["cols"])
+    _k8s_stub.queue_events(events)
+    fk.set_stream(events)
+    sink = ClusterApiClient("http://clusterapi.invalid")
+    w = PodWatcher("staging", sink=sink)
+    w.start_watching()
+    keep = po.transition_filter(fx["payloads"])
+    bodies = [json.loads(b) for b in sink.transport.bodies()]
+    assert len(bodies) == len(keep)
+    for b, k in zip(bodies, keep):
+        want = dict(fx["payloads"][k])
+        b.pop("event_timestamp"), want.pop("event_timestamp")       # wall clock, pod_watcher.py:199
+        assert b == want
