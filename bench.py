@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""Benchmark of the bulk phase-transition path: pod events/s classified on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c4] [--impl ours|reference]
+
+One step = one full replay (pte_run) of the workload's log: clear the uid dictionary, filter +
+intern + pack, LSD radix sort on the key, adjacent-diff + compaction, radix sort back to replay
+order, payload column assembly.  Default workload: BASELINE.json config 3 (the one the metric is
+quoted on): 1 B events / 10 M pods, uniform phase churn, staging filters (nothing dropped), per GPU.
+For N > 1 (launched under torchrun) every rank replays its own uid-hash shard of an N x larger
+log (weak scaling); the only collective is an NCCL all-gather of four counters per rank per step.
+
+Prints ONE JSON line (rank 0).  `value` is device time (CUDA events inside pte_run, max over
+ranks); `e2e` goes through host buffers: pte_ingest + pte_run + pte_fetch, wall clock.
+--impl reference times the CPU restatement of the reference's per-event loop (oracle/) instead.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 0x6B38735F77617463
+WORKLOADS = {
+    # name: (events per GPU, pods per GPU, dist, p_del, description)
+    "c2": (10_000_000, 100_000, 0, 0.0, "BASELINE config 2: synthetic replay 10M events / 100k pods, uniform phase churn"),
+    "c3": (1_000_000_000, 10_000_000, 0, 0.0, "BASELINE config 3: synthetic replay 1B events / 10M pods, uniform phase churn"),
+    "c4": (1_000_000_000, 10_000_000, 1, 0.05, "BASELINE config 4: skewed replay 1B events, octave-Zipf pod activity + 5% DELETED"),
+}
+METRIC = "pod events/sec classified"
+UNIT = "events/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--events", type=float, default=None, help="override events per GPU (parity/debug only)")
+    ap.add_argument("--pods", type=float, default=None)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the oracle's restatement of the reference's per-event loop, on the host cores
+# ----------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    """One process = one uid-hash shard of the sample, replayed the way the reference would:
+    per event should_process_event -> namespace list -> _extract_pod_data (pod_watcher.py:214-233),
+    then the last-known-phase layer.  Logging is off and event_timestamp is a constant."""
+    seed, n, pods, dist, p_del, shard, n_shards = args
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import fake_kubernetes as fk
+    from oracle import c_oracle
+    from oracle import podwatch_oracle as po
+    cols = c_oracle.generate(seed, n, pods, dist=dist, p_del=p_del, shard=shard, n_shards=n_shards)
+    events = [(e["type"], e["object"]) for e in fk.events_from_columns(cols, rich=False)]
+    t0 = time.perf_counter()
+    payloads = po.reference_trace("staging", {}, events, "1970-01-01T00:00:00")
+    keep = po.transition_filter(payloads)
+    dt = time.perf_counter() - t0
+    return n, len(keep), dt
+
+
+def cpu_reference_arm(wl, sample_per_core: int = 600_000):
+    """-> dict for `cpu_baseline` (Python port on all cores + C port on one core)."""
+    import multiprocessing as mp
+    from oracle import c_oracle
+    n_ev, n_pods, dist, p_del, _ = wl
+    cores = os.cpu_count() or 1
+    # same pod density as the workload: events/pods ratio kept, shards by uid hash like the GPU path
+    pods_per = max(1, int(sample_per_core * n_pods / n_ev))
+    jobs = [(SEED, sample_per_core, pods_per, dist, p_del, g, cores) for g in range(cores)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(cores) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    busy = max(r[2] for r in res)                    # slowest worker's replay time (set-up excluded)
+    total = sum(r[0] for r in res)
+    # C port, one thread, larger sample of the very same stream
+    cn = min(n_ev, 20_000_000)
+    cp = max(1, int(cn * n_pods / n_ev))
+    t1 = time.perf_counter()
+    c_oracle.generate_replay(SEED, cn, cp, dist=dist, p_del=p_del)
+    c_dt = time.perf_counter() - t1
+    return {
+        "value": total / busy, "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": "%d events (%d per core x %d uid-hash shards, %d pods each), Python restatement of "
+                  "handle_pod_event + transition layer, logging off; pool wall %.1fs" % (total, sample_per_core, cores, pods_per, wall),
+        "python_1core_events_per_s": res[0][0] / res[0][2],
+        "c_port_1thread_events_per_s": cn / c_dt,
+        "c_port_sample": "%d events / %d pods incl. generation" % (cn, cp),
+    }
+
+
+def run_reference(args, wl, rank):
+    if rank != 0:
+        return
+    cfg = {"workload": wl[4], "events_per_gpu": wl[0], "pods_per_gpu": wl[1], "filters": "staging (none)"}
+    vals, last = [], None
+    for s in range(args.warmup + args.steps):
+        last = cpu_reference_arm(wl, sample_per_core=60_000)
+        if s >= args.warmup:
+            vals.append(last["value"])
+    v = sum(vals) / len(vals)
+    last["value"] = v
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "python objects", "data": "synthetic", "config": cfg, "cpu_baseline": last,
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference arm = CPU restatement (oracle/) of the reference's per-event Python loop on a bounded "
+                "sample per step; /root/reference itself cannot travel to the GPU box",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    ev, pods, dist, p_del, desc = WORKLOADS[args.workload]
+    if args.events:
+        ev = int(args.events)
+    if args.pods:
+        pods = int(args.pods)
+    wl = (ev, pods, dist, p_del, desc)
+
+    if args.impl == "reference":
+        run_reference(args, wl, rank)
+        return
+
+    import numpy as np
+    from k8s_watcher_b200 import PhaseTransitionEngine
+    from k8s_watcher_b200.engine import PinnedBuffer
+
+    dist_t = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_t
+        torch.cuda.set_device(local)
+        dist_t.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist_t is not None:
+            dist_t.barrier()
+
+    eng = PhaseTransitionEngine(ev, pods, device=local)
+    if world > 1:
+        ids = [PhaseTransitionEngine.comm_unique_id() if rank == 0 else None]
+        dist_t.broadcast_object_list(ids, src=0)
+        eng.comm_init(ids[0], rank, world)
+    eng.set_filters(None)                                   # staging regime: every event reaches the sort
+    eng.generate(SEED, ev, pods, dist=dist, p_del=p_del, shard=rank, n_shards=world)
+
+    def step():
+        st = eng.run(dedupe=True)
+        t0 = time.perf_counter()
+        counts = eng.gather_counts() if world > 1 else None
+        return st, (time.perf_counter() - t0) * 1e3, counts
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    dev_ms = gather_ms = 0.0
+    pass_ms = pass_n = 0.0
+    launches = 0
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        st, g_ms, counts = step()
+        dev_ms += st["ms_total"]; gather_ms += g_ms
+        pass_ms += st["ms_pass_avg"] * st["n_passes"]; pass_n += st["n_passes"]
+        launches += st["n_launches"]
+    barrier()
+    wall_ms = (time.perf_counter() - wall0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    step_ms = (dev_ms + gather_ms) / args.steps
+    if world > 1:
+        import torch
+        t = torch.tensor([step_ms, wall_ms / args.steps], device="cuda", dtype=torch.float64)
+        dist_t.all_reduce(t, op=dist_t.ReduceOp.MAX)
+        step_ms, wall_step_ms = float(t[0]), float(t[1])
+        total_events = int(counts[:, 0].sum())
+        total_emitted = int(counts[:, 2].sum())
+    else:
+        wall_step_ms = wall_ms / args.steps
+        total_events, total_emitted = int(st["n_in"]), int(st["n_emitted"])
+
+    # ---- roofline of the dominant kernel: the radix scatter pass (8 B read + 8 B written per record)
+    roof = None
+    if pass_n:
+        # records moved per launch: key passes see n_survived records, order passes n_emitted
+        kp = _key_passes(pods)
+        op = int(st["n_passes"]) - kp
+        bytes_per_step = 16.0 * (kp * st["n_survived"] + op * st["n_emitted"])
+        peak, peak_src = _peak()
+        ach = bytes_per_step * args.steps / (pass_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "radix_pass_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "peak_source": peak_src, "traffic": _traffic(), "launches_per_step": int(st["n_passes"]),
+                "avg_launch_ms": pass_ms / pass_n, "algorithmic_bytes_per_launch": bytes_per_step / st["n_passes"],
+                "frac_of_8TBps_nominal": ach / 8000.0}
+
+    # ---- end to end through host buffers (rank-local; max over ranks)
+    e2e = None
+    if not args.no_e2e:
+        e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier)
+        if world > 1:
+            import torch
+            t = torch.tensor([e2e["ms_per_step"]], device="cuda", dtype=torch.float64)
+            dist_t.all_reduce(t, op=dist_t.ReduceOp.MAX)
+            e2e["ms_per_step"] = float(t[0])
+            b = torch.tensor([e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"]], device="cuda", dtype=torch.float64)
+            dist_t.all_reduce(b)
+            e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"] = int(b[0]), int(b[1])
+        e2e["value"] = total_events / (e2e["ms_per_step"] * 1e-3)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_reference_arm(wl)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": total_events / (step_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": desc, "events_per_gpu": ev, "pods_per_gpu": pods, "filters": "staging (none)",
+                       "dedupe": True, "shards": world, "l2": "inputs (30 GB log, 8 GB record buffers) far larger than the 126 MB L2",
+                       "seed": hex(SEED), "emitted_total": total_emitted, "wall_ms_per_step": wall_step_ms},
+            "stage_ms": {k: st[k] for k in ("ms_intern", "ms_sort_key", "ms_diff", "ms_sort_order", "ms_assemble")},
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if dist_t is not None:
+        dist_t.destroy_process_group()
+
+
+def _key_passes(pods: int) -> int:
+    cap = 256
+    while cap < int(pods / 0.6) + 1:
+        cap <<= 1
+    return ((cap - 1).bit_length() + 7) // 8
+
+
+def _peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get("radix_pass_kernel_dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+def _e2e(eng, args, np, PinnedBuffer, ev, barrier):
+    """pte_ingest (pinned host columns -> HBM) + pte_run + pte_fetch (all payload columns -> pinned host)."""
+    dts = (("uid_hi", np.uint64), ("uid_lo", np.uint64), ("rv", np.uint64), ("ns_id", np.uint32), ("phase", np.uint8),
+           ("type", np.uint8))
+    pins = {k: PinnedBuffer(ev, dt) for k, dt in dts}
+    host = eng.read_log(into={k: p.array for k, p in pins.items()})           # set-up, untimed
+    odts = dict(idx=np.uint32, rv=np.uint64, key=np.uint64, ns_id=np.uint32, phase=np.uint8, type=np.uint8)
+    opins = {k: PinnedBuffer(ev, dt) for k, dt in odts.items()}
+    out = {k: p.array for k, p in opins.items()}
+    eng.ingest(host); eng.run(); eng.fetch(into=out)                          # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        eng.ingest(host)
+        st = eng.run(dedupe=True)
+        got = eng.fetch(into=out)
+    ms = (time.perf_counter() - t0) * 1e3 / args.e2e_steps
+    barrier()
+    res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps,
+           "h2d_bytes_per_step": 30 * ev, "d2h_bytes_per_step": 26 * len(got),
+           "api": "pte_ingest + pte_run + pte_fetch (idx, rv, key, ns_id, phase, type) with pinned host buffers"}
+    for p in list(pins.values()) + list(opins.values()):
+        p.free()
+    return res
+
+
+if __name__ == "__main__":
+    main()
