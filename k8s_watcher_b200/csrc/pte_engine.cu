@@ -88,7 +88,7 @@ struct pte_engine {
     u64 *recA = nullptr, *recB = nullptr;
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
-    int pass_cfg = 0, pass_occ = 1, pass_tile = 4096;
+    int pass_cfg = 4, pass_occ = 1, pass_tile = 6144;
     Counters* ctr = nullptr;
     // filters
     u32* ns_bitmap = nullptr;
@@ -285,6 +285,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     } while (0)
 
     CKCU(cudaSetDevice(device));
+    if (const char* g = getenv("PTE_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g));
     CKCU(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     CKCU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(prepare_pass_cfg(h));

@@ -3,7 +3,7 @@
 //   radix_hist_kernel  one read of the records -> digit counts of every pass
 //   radix_pass_kernel  one scatter pass: read 8 B, write 8 B per record, single sweep.
 //                      Tiles are chained with a decoupled look-back over per-tile digit
-//                      counts, digits are ranked inside a warp with MATCH.ANY + popc
+//                      counts, digits are ranked inside a warp with ballot-built peer masks + popc
 //                      (stable: lower lanes first), and every tile is re-ordered in shared
 //                      memory first so that global writes are runs of consecutive records.
 //
@@ -103,7 +103,7 @@ struct RadixPassSmem {
 };
 
 template <int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? 4 : 2))
 radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ n_ptr, u64 n_fixed,
                   int shift, u32 mask, const u32* __restrict__ hist, u32* __restrict__ lookback,
                   u32* __restrict__ ticket) {
@@ -138,12 +138,25 @@ radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* 
             u32 t = wbase + k * 32;
             key[k] = t < tile_valid ? __ldcs(in + tile_base + t) : ~0ull;
         }
-        // (2) rank inside the warp, in record order, against the warp's private digit counters
+        // (2) rank inside the warp, in record order, against the warp's private digit counters.
+        // Peers (lanes holding the same digit) come from one ballot per digit bit: MATCH.ANY would do
+        // it in one instruction but runs on the ADU pipe, which then bounds the whole pass (profiles/).
+        const bool full_tile = tile_valid == TILE;
 #pragma unroll
         for (int k = 0; k < ITEMS; k++) {
-            const bool valid = wbase + k * 32 < tile_valid;
-            const u32 d = valid ? ((u32)(key[k] >> shift) & mask) : (u32)kRadix;
-            const u32 peers = __match_any_sync(0xffffffffu, d);
+            const bool valid = full_tile || wbase + k * 32 < tile_valid;
+            const u32 d = (u32)(key[k] >> shift) & mask;
+            u32 peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const bool bit = (d >> b) & 1u;
+                const u32 m = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? m : ~m;
+            }
+            if (!full_tile) {
+                const u32 vm = __ballot_sync(0xffffffffu, valid);
+                peers &= valid ? vm : ~vm;
+            }
             const u32 before = peers & lt;
             u32 base = 0;
             if (before == 0 && valid) {
