@@ -68,9 +68,9 @@ typedef struct pte_stats {
     float ms_total;         /* device time of this pte_run, CUDA events on the engine stream */
     float ms_intern;        /* filter + uid interning + record packing */
     float ms_sort_key;      /* LSD radix passes on the interned key */
-    float ms_diff;          /* segmented adjacent-diff + compaction */
-    float ms_sort_order;    /* LSD radix passes restoring replay order */
-    float ms_assemble;      /* payload column assembly */
+    float ms_diff;          /* segmented adjacent-diff -> emit bitmap */
+    float ms_sort_order;    /* always 0 since replay order is restored by the bitmap scan in ms_assemble */
+    float ms_assemble;      /* bitmap scan + compaction in replay order + payload columns */
     float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
     uint32_t n_passes;      /* radix scatter passes run */
     uint32_t reserved;
@@ -133,7 +133,7 @@ int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv,
 /* ---- the hot path --------------------------------------------------------- */
 
 /* Replay the device-resident log: filters -> uid interning -> LSD radix sort on (key, rv) ->
- * segmented adjacent-diff + compaction -> restore replay order -> payload columns.
+ * segmented adjacent-diff -> emit bitmap -> scan of the bitmap in replay order -> payload columns.
  * dedupe == 0: every event that would reach the POST site (pod_watcher.py:232-236), the R-trace.
  * dedupe != 0: only phase transitions and DELETED tombstones (the last-known-phase layer the
  *              reference's README describes but pod_watcher.py does not implement), the T-trace.

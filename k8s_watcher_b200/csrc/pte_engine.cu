@@ -85,7 +85,8 @@ struct pte_engine {
     u64 table_cap = 0;
     RecLayout L{};
     // sort
-    u64 *recA = nullptr, *recB = nullptr;
+    u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // arrival-ordered records + sort ping-pong
+    u32 *origin = nullptr, *bitmap = nullptr;                // compacted position -> arrival index; emit bits
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
     int pass_cfg = 4, pass_occ = 1, pass_tile = 6144;
@@ -160,10 +161,11 @@ int prepare_pass_cfg(pte_engine* h) {
     return PTE_OK;
 }
 
-// Stable LSD sort of the records in `src` on bits [bit_lo, bit_hi); `other` is the ping-pong buffer.
+// Stable LSD sort of the records in `src` on bits [bit_lo, bit_hi).  `src` is left intact: the first
+// pass scatters into `x`, later passes ping-pong between `x` and `y`.
 // n is read on the device from n_ptr when given (n_upper bounds it for sizing), else n_upper.
 // On return *result points at the buffer that holds the sorted records.
-int sort_field(pte_engine* h, u64* src, u64* other, const u64* n_ptr, u64 n_upper, int bit_lo, int bit_hi,
+int sort_field(pte_engine* h, u64* src, u64* x, u64* y, const u64* n_ptr, u64 n_upper, int bit_lo, int bit_hi,
                u64** result) {
     *result = src;
     if (bit_hi <= bit_lo || n_upper == 0) return PTE_OK;
@@ -176,7 +178,7 @@ int sort_field(pte_engine* h, u64* src, u64* other, const u64* n_ptr, u64 n_uppe
     h->n_launches++;
     const u64 tiles = (n_upper + h->pass_tile - 1) / h->pass_tile;
     if (tiles * kRadix > h->lookback_words) FAIL(h, PTE_ERR_CAPACITY, "look-back buffer too small");
-    u64 *a = src, *b = other;
+    u64 *a = src, *b = x;
     for (int p = 0; p < passes; p++) {
         const int shift = bit_lo + 8 * p;
         const int rem = bit_hi - shift;
@@ -194,7 +196,7 @@ int sort_field(pte_engine* h, u64* src, u64* other, const u64* n_ptr, u64 n_uppe
         int rc = launch_pass_cfg(h, a, b, n_ptr, n_upper, shift, mask, h->hist + p * kRadix);
         if (rc) return rc;
         CK(h, cudaEventRecord(pe.second, h->stream));
-        std::swap(a, b);
+        if (p == 0) { a = x; b = y; } else std::swap(a, b);
     }
     *result = a;
     return PTE_OK;
@@ -232,7 +234,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->origin, h->bitmap, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv};
     for (void* b : bufs) if (b) cudaFree(b);
@@ -294,7 +296,8 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKC(dev_alloc(h, &h->uid_hi, c)); CKC(dev_alloc(h, &h->uid_lo, c)); CKC(dev_alloc(h, &h->rv, c));
     CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
     CKC(dev_alloc(h, &h->table, h->table_cap));
-    CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c));
+    CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c)); CKC(dev_alloc(h, &h->recC, c));
+    CKC(dev_alloc(h, &h->origin, c)); CKC(dev_alloc(h, &h->bitmap, c / 32));
     // look-back words: one per (radix tile, digit); also one per intern tile
     u64 min_tile = 2048;
     h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
@@ -435,7 +438,7 @@ int pte_generate(pte_handle h, const pte_gen_params* p) {
     CK(h, cudaGetLastError());
     u64* sorted = nullptr;
     h->pass_ev_used = 0;
-    rc = sort_field(h, h->recA, h->recB, nullptr, n, a.L.key_shift(), a.L.key_shift() + a.L.key_bits, &sorted);
+    rc = sort_field(h, h->recA, h->recB, h->recC, nullptr, n, a.L.key_shift(), a.L.key_shift() + a.L.key_bits, &sorted);
     if (rc) return rc;
     gen_type_kernel<<<grid, 256, 0, h->stream>>>(sorted, n, a.L, h->type);
     CK(h, cudaGetLastError());
@@ -455,11 +458,11 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
     CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
     const bool filtered = h->critical_only || h->ns_filter_on;
-    u64* final_rec = h->recA;
     if (n) {
         InternArgs a;
         a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
         a.n = n; a.table = h->table; a.table_mask = (u32)(h->table_cap - 1); a.L = h->L; a.rec_out = h->recA;
+        a.origin = h->origin;
         a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
         a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
         const u64 tiles = (n + kInternTile - 1) / kInternTile;
@@ -474,21 +477,30 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         h->n_launches++;
     }
     CK(h, cudaEventRecord(h->ev[1], st));
+    AssembleArgs as;
+    as.rec = h->recA; as.origin = filtered ? h->origin : nullptr; as.bitmap = h->bitmap; as.rv = h->rv; as.ns = h->ns;
+    as.L = h->L; as.ctr = h->ctr; as.lookback = h->lookback;
+    as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_key = h->out_key; as.out_ns = h->out_ns;
+    as.out_phase = h->out_phase; as.out_type = h->out_type;
     if (n && dedupe) {
         u64* sorted = nullptr;
-        int rc = sort_field(h, h->recA, h->recB, &h->ctr->n_survived, n, h->L.key_shift(),
+        int rc = sort_field(h, h->recA, h->recB, h->recC, &h->ctr->n_survived, n, h->L.key_shift(),
                             h->L.key_shift() + h->L.key_bits, &sorted);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[2], st));
-        u64* other = sorted == h->recA ? h->recB : h->recA;
-        int grid = (int)std::min<u64>((n + kDiffThreads * kDiffItems - 1) / (kDiffThreads * kDiffItems), (u64)h->num_sms * 8);
-        diff_compact_kernel<<<grid, kDiffThreads, 0, st>>>(sorted, other, h->L, h->ctr);
+        CK(h, cudaMemsetAsync(h->bitmap, 0, ((n + 31) / 32) * sizeof(u32), st));
+        int grid = (int)std::min<u64>((n + 511) / 512, (u64)h->num_sms * 16);
+        diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, h->bitmap, h->L, h->ctr);
         CK(h, cudaGetLastError());
         h->n_launches++;
         CK(h, cudaEventRecord(h->ev[3], st));
-        rc = sort_field(h, other, sorted, &h->ctr->n_emitted, n, 8, 8 + h->L.idx_bits, &final_rec);
-        if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[4], st));
+        const u64 tiles = (n + kAsmTile - 1) / kAsmTile;
+        CK(h, cudaMemsetAsync(h->lookback, 0, tiles * sizeof(u32), st));
+        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 6);
+        assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
+        CK(h, cudaGetLastError());
+        h->n_launches++;
     } else {
         // R-trace: every survivor is emitted, already in replay order
         CK(h, cudaEventRecord(h->ev[2], st));
@@ -496,16 +508,12 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         CK(h, cudaMemcpyAsync(&h->ctr->n_tombstones, &h->ctr->n_del_survived, sizeof(u64), cudaMemcpyDeviceToDevice, st));
         CK(h, cudaEventRecord(h->ev[3], st));
         CK(h, cudaEventRecord(h->ev[4], st));
-    }
-    if (n) {
-        AssembleArgs a;
-        a.rec = final_rec; a.n_ptr = &h->ctr->n_emitted; a.rv = h->rv; a.ns = h->ns; a.L = h->L;
-        a.out_idx = h->out_idx; a.out_rv = h->out_rv; a.out_key = h->out_key; a.out_ns = h->out_ns;
-        a.out_phase = h->out_phase; a.out_type = h->out_type;
-        int grid = (int)std::min<u64>((n + 1023) / 1024, (u64)h->num_sms * 8);
-        assemble_kernel<<<grid, 256, 0, st>>>(a);
-        CK(h, cudaGetLastError());
-        h->n_launches++;
+        if (n) {
+            int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+            assemble_all_kernel<<<grid, 256, 0, st>>>(as);
+            CK(h, cudaGetLastError());
+            h->n_launches++;
+        }
     }
     CK(h, cudaEventRecord(h->ev[5], st));
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -601,7 +609,7 @@ int pte_debug_sort_u64(pte_handle h, uint64_t* records, uint64_t n, int bit_lo, 
     CK(h, cudaMemcpyAsync(h->recA, records, n * 8, cudaMemcpyHostToDevice, h->stream));
     u64* sorted = nullptr;
     h->pass_ev_used = 0;
-    int rc = sort_field(h, h->recA, h->recB, nullptr, n, bit_lo, bit_hi, &sorted);
+    int rc = sort_field(h, h->recA, h->recB, h->recC, nullptr, n, bit_lo, bit_hi, &sorted);
     if (rc) return rc;
     CK(h, cudaMemcpyAsync(records, sorted, n * 8, cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));

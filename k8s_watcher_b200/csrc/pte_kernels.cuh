@@ -1,7 +1,7 @@
 // Device kernels of the replay path other than the sort:
 //   intern_pack_kernel   filters (pod_watcher.py:204-212, :226-229) + uid interning + record packing
-//   diff_compact_kernel  segmented adjacent-diff + ballot/popc compaction
-//   assemble_kernel      payload columns of the emitted records, in replay order (pod_watcher.py:232-236)
+//   diff_flag_kernel     segmented adjacent-diff on the key-sorted records -> emit bitmap
+//   assemble_*_kernel    scan/compaction of the bitmap in replay order -> payload columns (pod_watcher.py:232-236)
 //   digest_kernel        order-sensitive digest for large-scale parity
 //   gen_* kernels        synthetic replay logs (spec in include/pte.h)
 #pragma once
@@ -21,7 +21,7 @@ struct Counters {
     u64 digest;
     u32 n_pods;
     u32 flags;
-    u32 ticket[4];         // tile tickets: [0] intern, [1] radix pass (reset per pass), [2..3] spare
+    u32 ticket[4];         // tile tickets: [0] intern, [1] radix pass (reset per pass), [2] assemble, [3] spare
 };
 
 __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo, u64 val_hi, u64 val_lo) {
@@ -47,11 +47,11 @@ static constexpr int kMaxProbe = 2048;
 // A plain 16-byte load may see a slot as empty when it is not (stale line), or half-written
 // (0:0 -> hi:lo is the only transition a slot ever makes).  Either shows up as a zero half,
 // and then the 128-bit CAS -- which returns the true content -- decides.
-__device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u64 hi, u64 lo, u32& inserted,
-                                          u32* __restrict__ flags) {
-    u32 sl = (u32)mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull)) & mask;
+// `v` is the content of slot `sl` as loaded by the caller (so that a thread can have the first
+// probe of all its events in flight before it resolves any of them).
+__device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u64 hi, u64 lo, u32 sl, ulonglong2 v,
+                                          u32& inserted, u32* __restrict__ flags) {
     for (int p = 0; p < kMaxProbe; ++p) {
-        ulonglong2 v = *reinterpret_cast<const ulonglong2*>(table + sl);
         if (v.x == 0 || v.y == 0) {
             ulonglong2 old = cas128(table + sl, 0, 0, hi, lo);
             if (old.x == 0 && old.y == 0) { inserted++; return sl; }
@@ -60,9 +60,13 @@ __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u6
             return sl;
         }
         sl = (sl + 1) & mask;
+        v = *reinterpret_cast<const ulonglong2*>(table + sl);
     }
     atomicOr(flags, kFlagTableFull);
     return 0;
+}
+__device__ __forceinline__ u32 uid_home_slot(u64 hi, u64 lo, u32 mask) {
+    return (u32)mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull)) & mask;
 }
 
 struct InternArgs {
@@ -72,6 +76,7 @@ struct InternArgs {
     Slot* table; u32 table_mask;
     RecLayout L;
     u64* rec_out;
+    u32* origin;       // FILTERED only: arrival index of the record at each compacted position
     const u32* ns_bitmap; u32 ns_words; int ns_filter_on; int critical_only;
     Counters* ctr;
     u32* lookback;     // one word per tile (FILTERED only)
@@ -82,8 +87,10 @@ static constexpr int kInternPerThread = 4;
 static constexpr int kInternTile = kInternThreads * kInternPerThread;
 
 // One event per (thread, k): thread t of a tile owns events 4t..4t+3, loaded with 16-byte vectors.
-// FILTERED == false: no predicate is active, record i goes to rec_out[i].
-// FILTERED == true : survivors are compacted in arrival order (tile totals chained by look-back).
+// The record's position field is the record's place in rec_out:
+// FILTERED == false: no predicate is active, event i goes to rec_out[i].
+// FILTERED == true : survivors are compacted in arrival order (tile totals chained by look-back)
+//                    and origin[] remembers where each one came from.
 template <bool FILTERED>
 __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs a) {
     __shared__ u32 s_tot[8];
@@ -91,14 +98,17 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     const u32 tid = threadIdx.x, lane = tid & 31;
     u32 inserted = 0, del_surv = 0, flags = 0;
     if (!FILTERED && blockIdx.x == 0 && tid == 0) a.ctr->n_survived = a.n;
+    const u32 n_tiles = (u32)((a.n + kInternTile - 1) / kInternTile);
 
-    for (;;) {
-        __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket[0], 1u);
-        __syncthreads();
-        const u32 tile = s_tile;
+    for (u32 tile = blockIdx.x;; tile += gridDim.x) {
+        if (FILTERED) {            // look-back needs tiles handed out in order
+            __syncthreads();
+            if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket[0], 1u);
+            __syncthreads();
+            tile = s_tile;
+        }
+        if (tile >= n_tiles) break;
         const u64 i0 = (u64)tile * kInternTile + (u64)tid * kInternPerThread;
-        if ((u64)tile * kInternTile >= a.n) break;
 
         u64 hi[4], lo[4], rv[4];
         u32 ns[4], ph[4], ty[4];
@@ -109,8 +119,18 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
             p = reinterpret_cast<const ulonglong2*>(a.uid_lo + i0);
             x = __ldcs(p); y = __ldcs(p + 1);
             lo[0] = x.x; lo[1] = x.y; lo[2] = y.x; lo[3] = y.y;
-            p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
-            x = __ldcs(p); y = __ldcs(p + 1);
+        }
+        // first probe of all four events in flight before anything else is looked at
+        u32 sl[4];
+        ulonglong2 pv[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            sl[k] = uid_home_slot(hi[k], lo[k], a.table_mask);
+            pv[k] = *reinterpret_cast<const ulonglong2*>(a.table + sl[k]);
+        }
+        {
+            const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
+            ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
             rv[0] = x.x; rv[1] = x.y; rv[2] = y.x; rv[3] = y.y;
             uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.ns + i0));
             ns[0] = q.x; ns[1] = q.y; ns[2] = q.z; ns[3] = q.w;
@@ -169,7 +189,7 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
                     st_relaxed_u32(a.lookback + tile, kLbInclusive | (excl + total));
                 }
                 s_tile_excl = excl;
-                if ((u64)(tile + 1) * kInternTile >= a.n) a.ctr->n_survived = excl + total;   // last tile
+                if (tile + 1 == n_tiles) a.ctr->n_survived = excl + total;   // last tile
             }
             __syncthreads();
             dst = (u64)s_tile_excl + local;
@@ -179,16 +199,14 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         for (int k = 0; k < 4; k++) {
             rec[k] = 0;
             if (keep[k]) {
-                u32 sl = intern_uid(a.table, a.table_mask, hi[k], lo[k], inserted, &a.ctr->flags);
-                rec[k] = rec_pack(a.L, sl, i0 + k, ty[k], ph[k]);
+                u32 slot = intern_uid(a.table, a.table_mask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags);
+                const u64 pos = FILTERED ? dst : i0 + k;
+                rec[k] = rec_pack(a.L, slot, pos, ty[k], ph[k]);
                 del_surv += ty[k] == kTypeDeleted;
+                if (FILTERED) { a.rec_out[dst] = rec[k]; a.origin[dst] = (u32)(i0 + k); dst++; }
             }
         }
-        if (FILTERED) {
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                if (keep[k]) a.rec_out[dst++] = rec[k];
-        } else {
+        if (!FILTERED) {
             // buffers are padded to a tile multiple, so the full 32 bytes are always writable
             ulonglong2* o = reinterpret_cast<ulonglong2*>(a.rec_out + i0);
             o[0] = make_ulonglong2(rec[0], rec[1]);
@@ -206,114 +224,129 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     }
 }
 
-// ---- segmented adjacent-diff + compaction -----------------------------------
-// Input: survivors sorted by (key, arrival).  A record is emitted iff it is a DELETED, opens its
+// ---- segmented adjacent-diff -> emit bitmap ----------------------------------
+// Input: survivors sorted by (key, position).  A record is emitted iff it is a DELETED, opens its
 // key's segment, follows a DELETED of the same key, or carries a different effective phase than
-// its predecessor -- the bulk form of the sequential last-known-phase rule.
-static constexpr int kDiffThreads = 256;
-static constexpr int kDiffItems = 8;
-
-__global__ void __launch_bounds__(kDiffThreads)
-diff_compact_kernel(const u64* __restrict__ in, u64* __restrict__ out, RecLayout L, Counters* __restrict__ ctr) {
-    __shared__ u32 s_cnt[kDiffItems][kDiffThreads / 32];
-    __shared__ u32 s_base;
-    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const u32 lt = lanemask_lt();
+// its predecessor -- the bulk form of the sequential last-known-phase rule (SURVEY.md 8a row 7).
+// Emission sets bit `position` of a bitmap (one bit per record of the arrival-ordered buffer;
+// 1 B events = 125 MB, which the 126 MB L2 mostly keeps), so that the payload stage can walk
+// arrival order and needs no second sort.  Two records per thread (one 16-byte load).
+__global__ void __launch_bounds__(256)
+diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout L, Counters* __restrict__ ctr) {
     const u64 n = ctr->n_survived;
     const u32 ks = L.key_shift();
-    constexpr int TILE = kDiffThreads * kDiffItems;
+    const u32 lane = threadIdx.x & 31;
     u32 tomb = 0;
-    for (u64 base = (u64)blockIdx.x * TILE; base < n; base += (u64)gridDim.x * TILE) {
-        u64 cur[kDiffItems];
-        u32 ballot[kDiffItems];
+    const u64 stride = (u64)gridDim.x * blockDim.x * 2;
+    // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffle
+    for (u64 wb = ((u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) * 2; wb < n; wb += stride) {
+        const u64 i = wb + lane * 2;
+        const ulonglong2 c = __ldcs(reinterpret_cast<const ulonglong2*>(in + i));   // padded: readable past n
+        u64 p = __shfl_up_sync(0xffffffffu, c.y, 1);
+        if (lane == 0) p = i > 0 ? in[i - 1] : ~c.x;                                  // ~c.x: a different key
+        const u64 r[2] = {c.x, c.y};
 #pragma unroll
-        for (int k = 0; k < kDiffItems; k++) {
-            const u64 i = base + (u64)k * kDiffThreads + tid;
-            bool emit = false;
-            cur[k] = 0;
-            if (i < n) {
-                const u64 c = in[i];
-                cur[k] = c;
-                bool head = true, prev_del = false, differ = false;
-                if (i > 0) {
-                    const u64 p = in[i - 1];   // the neighbour's record: same line, served by L1
-                    head = (p >> ks) != (c >> ks);
-                    prev_del = rec_type(p) == kTypeDeleted;
-                    differ = eff_phase(rec_phase(p)) != eff_phase(rec_phase(c));
+        for (int k = 0; k < 2; k++) {
+            if (i + k < n) {
+                const u64 cur = r[k];
+                const bool head = (p >> ks) != (cur >> ks);
+                const bool emit = rec_type(cur) == kTypeDeleted || head || rec_type(p) == kTypeDeleted ||
+                                  eff_phase(rec_phase(p)) != eff_phase(rec_phase(cur));
+                if (emit) {
+                    const u64 pos = rec_idx(L, cur);
+                    atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
+                    tomb += rec_type(cur) == kTypeDeleted;
                 }
-                emit = rec_type(c) == kTypeDeleted || head || prev_del || differ;
-                tomb += emit && rec_type(c) == kTypeDeleted;
+                p = cur;
             }
-            ballot[k] = __ballot_sync(0xffffffffu, emit);
-            if (lane == 0) s_cnt[k][warp] = __popc(ballot[k]);
         }
-        __syncthreads();
-        if (warp == 0) {
-            // exclusive scan of the 64 (item, warp) counts: two per lane
-            u32 a = (&s_cnt[0][0])[2 * lane], b = (&s_cnt[0][0])[2 * lane + 1];
-            u32 sum = a + b, inc = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                u32 t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
-            }
-            u32 total = __shfl_sync(0xffffffffu, inc, 31);
-            u32 gbase = 0;
-            if (lane == 0 && total) gbase = (u32)atomicAdd(&ctr->n_emitted, (u64)total);
-            gbase = __shfl_sync(0xffffffffu, gbase, 0);
-            (&s_cnt[0][0])[2 * lane] = inc - sum;
-            (&s_cnt[0][0])[2 * lane + 1] = inc - sum + a;
-            if (lane == 0) s_base = gbase;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < kDiffItems; k++) {
-            if ((ballot[k] >> lane) & 1u)
-                out[(u64)s_base + s_cnt[k][warp] + __popc(ballot[k] & lt)] = cur[k];
-        }
-        __syncthreads();
     }
     tomb = __reduce_add_sync(0xffffffffu, tomb);
     if (lane == 0 && tomb) atomicAdd(&ctr->n_tombstones, (u64)tomb);
 }
 
 // ---- payload columns --------------------------------------------------------
-// Emitted records, already in replay order, -> the columns a sink needs.  Four records per
-// thread so that every store is a 16-byte vector (or a 4-byte word for the two byte columns).
+// Emitted records -> the columns a sink needs (idx, rv, key, ns_id, phase, type), in replay order.
 struct AssembleArgs {
-    const u64* rec; const u64* n_ptr;
+    const u64* rec;        // arrival-ordered records (rec_out of intern_pack_kernel)
+    const u32* origin;     // compacted position -> arrival index (NULL: identity)
+    const u32* bitmap;     // emit bit per position (bitmap kernel only)
     const u64* rv; const u32* ns;
     RecLayout L;
+    Counters* ctr;
+    u32* lookback;
     u32* out_idx; u64* out_rv; u64* out_key; u32* out_ns; u8* out_phase; u8* out_type;
 };
 
-__global__ void __launch_bounds__(256) assemble_kernel(AssembleArgs a) {
-    const u64 n = *a.n_ptr;
-    const u64 stride = (u64)gridDim.x * blockDim.x * 4;
-    for (u64 i = ((u64)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
-        const ulonglong2* rp = reinterpret_cast<const ulonglong2*>(a.rec + i);
-        ulonglong2 r01 = rp[0], r23 = rp[1];      // padded buffers: reading past n is harmless
-        u64 r[4] = {r01.x, r01.y, r23.x, r23.y};
-        u32 idx[4], ns[4], ph = 0, ty = 0;
-        u64 rv[4], key[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const bool ok = i + k < n;
-            idx[k] = ok ? (u32)rec_idx(a.L, r[k]) : 0;
-            rv[k] = ok ? __ldg(a.rv + idx[k]) : 0;
-            ns[k] = ok ? __ldg(a.ns + idx[k]) : 0;
-            key[k] = ok ? rec_key(a.L, r[k]) : 0;
-            ph |= (ok ? rec_phase(r[k]) : 0u) << (8 * k);
-            ty |= (ok ? rec_type(r[k]) : 0u) << (8 * k);
+__device__ __forceinline__ void assemble_one(const AssembleArgs& a, u64 pos, u64 j) {
+    const u64 r = a.rec[pos];
+    const u32 idx = a.origin ? a.origin[pos] : (u32)pos;
+    a.out_idx[j] = idx;
+    a.out_rv[j] = __ldg(a.rv + idx);
+    a.out_key[j] = rec_key(a.L, r);
+    a.out_ns[j] = __ldg(a.ns + idx);
+    a.out_phase[j] = (u8)rec_phase(r);
+    a.out_type[j] = (u8)rec_type(r);
+}
+
+// R-trace: every survivor is emitted, position == output row.
+__global__ void __launch_bounds__(256) assemble_all_kernel(AssembleArgs a) {
+    const u64 n = a.ctr->n_survived;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        assemble_one(a, i, i);
+}
+
+// T-trace: stable compaction of the positions whose emit bit is set.  A tile is 256 bitmap words
+// (8192 positions), one word per thread; tile totals are chained by a decoupled look-back; the
+// tile's emitted positions are listed in shared memory so that the column writes are coalesced.
+static constexpr int kAsmTile = 256 * 32;
+
+__global__ void __launch_bounds__(256) assemble_bitmap_kernel(AssembleArgs a) {
+    __shared__ u32 s_pos[kAsmTile];
+    __shared__ u32 s_tot[8];
+    __shared__ u32 s_tile, s_excl, s_total;
+    const u32 tid = threadIdx.x;
+    const u64 n = a.ctr->n_survived;
+    const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket[2], 1u);
+        __syncthreads();
+        const u32 tile = s_tile;
+        if (tile >= n_tiles) break;
+        const u64 wbase = (u64)tile * 256 + tid;          // bitmap word of this thread
+        u32 w = wbase * 32 < n ? __ldcs(a.bitmap + wbase) : 0u;
+        u32 total;
+        u32 local = excl_scan_256(__popc(w), s_tot, &total);
+        if (tid == 0) {
+            u32 excl = 0;
+            if (tile == 0) {
+                st_relaxed_u32(a.lookback, kLbInclusive | total);
+            } else {
+                st_relaxed_u32(a.lookback + tile, kLbPartial | total);
+                u32 t = tile - 1;
+                for (;;) {
+                    u32 v = ld_relaxed_u32(a.lookback + t);
+                    if ((v >> 30) == 0) { __nanosleep(20); continue; }
+                    excl += v & kLbValue;
+                    if ((v >> 30) == 2) break;
+                    t--;
+                }
+                st_relaxed_u32(a.lookback + tile, kLbInclusive | (excl + total));
+            }
+            s_excl = excl; s_total = total;
+            if (tile + 1 == n_tiles) a.ctr->n_emitted = (u64)excl + total;
         }
-        *reinterpret_cast<uint4*>(a.out_idx + i) = make_uint4(idx[0], idx[1], idx[2], idx[3]);
-        *reinterpret_cast<uint4*>(a.out_ns + i) = make_uint4(ns[0], ns[1], ns[2], ns[3]);
-        reinterpret_cast<ulonglong2*>(a.out_rv + i)[0] = make_ulonglong2(rv[0], rv[1]);
-        reinterpret_cast<ulonglong2*>(a.out_rv + i)[1] = make_ulonglong2(rv[2], rv[3]);
-        reinterpret_cast<ulonglong2*>(a.out_key + i)[0] = make_ulonglong2(key[0], key[1]);
-        reinterpret_cast<ulonglong2*>(a.out_key + i)[1] = make_ulonglong2(key[2], key[3]);
-        *reinterpret_cast<u32*>(a.out_phase + i) = ph;
-        *reinterpret_cast<u32*>(a.out_type + i) = ty;
+        const u32 p0 = tid * 32;
+        while (w) {
+            const u32 b = __ffs(w) - 1;
+            w &= w - 1;
+            s_pos[local++] = p0 + b;
+        }
+        __syncthreads();
+        const u64 tbase = (u64)tile * kAsmTile, obase = s_excl;
+        const u32 cnt = s_total;
+        for (u32 j = tid; j < cnt; j += 256) assemble_one(a, tbase + s_pos[j], obase + j);
     }
 }
 
