@@ -90,6 +90,8 @@ struct pte_engine {
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
     int pass_cfg = 4, pass_occ = 1, pass_tile = 6144;
+    u64 diff_round_bytes = 64ull << 20;      // bitmap bytes one diff round may touch
+    bool key_valid = false;                  // out_key holds the keys of the last run
     Counters* ctr = nullptr;
     // filters
     u32* ns_bitmap = nullptr;
@@ -268,6 +270,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
         delete h;
         return PTE_ERR_CAPACITY;
     }
+    if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
     const char* cfg = getenv("PTE_PASS_CFG");
     if (cfg) h->pass_cfg = std::min(std::max(atoi(cfg), 0), kNumPassCfgs - 1);
 
@@ -478,9 +481,10 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     }
     CK(h, cudaEventRecord(h->ev[1], st));
     AssembleArgs as;
-    as.rec = h->recA; as.origin = filtered ? h->origin : nullptr; as.bitmap = h->bitmap; as.rv = h->rv; as.ns = h->ns;
-    as.L = h->L; as.ctr = h->ctr; as.lookback = h->lookback;
-    as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_key = h->out_key; as.out_ns = h->out_ns;
+    as.origin = filtered ? h->origin : nullptr; as.bitmap = h->bitmap;
+    as.rv = h->rv; as.ns = h->ns; as.phase = h->phase; as.type = h->type;
+    as.ctr = h->ctr; as.lookback = h->lookback;
+    as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_ns = h->out_ns;
     as.out_phase = h->out_phase; as.out_type = h->out_type;
     if (n && dedupe) {
         u64* sorted = nullptr;
@@ -490,9 +494,15 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         CK(h, cudaEventRecord(h->ev[2], st));
         CK(h, cudaMemsetAsync(h->bitmap, 0, ((n + 31) / 32) * sizeof(u32), st));
         int grid = (int)std::min<u64>((n + 511) / 512, (u64)h->num_sms * 16);
-        diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, h->bitmap, h->L, h->ctr);
-        CK(h, cudaGetLastError());
-        h->n_launches++;
+        // rounds: each touches a slice of the bitmap small enough to stay in L2
+        const u64 bits_per_round = h->diff_round_bytes * 8;
+        const u64 rounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
+        const u64 span = round_up((n + rounds - 1) / rounds, 32);
+        for (u64 r = 0; r < rounds; r++) {
+            diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, h->bitmap, h->L, h->ctr, r * span, std::min(n, (r + 1) * span));
+            CK(h, cudaGetLastError());
+            h->n_launches++;
+        }
         CK(h, cudaEventRecord(h->ev[3], st));
         CK(h, cudaEventRecord(h->ev[4], st));
         const u64 tiles = (n + kAsmTile - 1) / kAsmTile;
@@ -521,6 +531,7 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     int rc = check_flags(h, h->last.flags);
     if (rc) return rc;
     h->has_run = true;
+    h->key_valid = false;
     if (out) {
         memset(out, 0, sizeof(*out));
         out->n_in = n; out->n_survived = h->last.n_survived; out->n_emitted = h->last.n_emitted;
@@ -556,7 +567,16 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
         cudaStream_t st = h->stream;
         if (idx) CK(h, cudaMemcpyAsync(idx, h->out_idx, n * 4, cudaMemcpyDeviceToHost, st));
         if (rv) CK(h, cudaMemcpyAsync(rv, h->out_rv, n * 8, cudaMemcpyDeviceToHost, st));
-        if (key) CK(h, cudaMemcpyAsync(key, h->out_key, n * 8, cudaMemcpyDeviceToHost, st));
+        if (key) {
+            if (!h->key_valid) {
+                int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+                key_lookup_kernel<<<grid, 256, 0, st>>>(h->out_idx, n, h->uid_hi, h->uid_lo, h->table,
+                                                        (u32)(h->table_cap - 1), h->out_key);
+                CK(h, cudaGetLastError());
+                h->key_valid = true;
+            }
+            CK(h, cudaMemcpyAsync(key, h->out_key, n * 8, cudaMemcpyDeviceToHost, st));
+        }
         if (ns_id) CK(h, cudaMemcpyAsync(ns_id, h->out_ns, n * 4, cudaMemcpyDeviceToHost, st));
         if (phase) CK(h, cudaMemcpyAsync(phase, h->out_phase, n, cudaMemcpyDeviceToHost, st));
         if (type) CK(h, cudaMemcpyAsync(type, h->out_type, n, cudaMemcpyDeviceToHost, st));

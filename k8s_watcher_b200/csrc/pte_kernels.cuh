@@ -209,8 +209,8 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         if (!FILTERED) {
             // buffers are padded to a tile multiple, so the full 32 bytes are always writable
             ulonglong2* o = reinterpret_cast<ulonglong2*>(a.rec_out + i0);
-            o[0] = make_ulonglong2(rec[0], rec[1]);
-            o[1] = make_ulonglong2(rec[2], rec[3]);
+            __stcs(o, make_ulonglong2(rec[0], rec[1]));       // streaming: leave L2 to the dictionary
+            __stcs(o + 1, make_ulonglong2(rec[2], rec[3]));
         }
     }
     // one atomic per warp for the run-wide counters
@@ -231,8 +231,12 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
 // Emission sets bit `position` of a bitmap (one bit per record of the arrival-ordered buffer;
 // 1 B events = 125 MB, which the 126 MB L2 mostly keeps), so that the payload stage can walk
 // arrival order and needs no second sort.  Two records per thread (one 16-byte load).
+// One launch covers the positions [pos_lo, pos_hi): the host splits the position space into rounds so
+// that the slice of the bitmap a round touches stays resident in L2 (re-reading the records for
+// every round is cheaper than letting the atomics miss).
 __global__ void __launch_bounds__(256)
-diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout L, Counters* __restrict__ ctr) {
+diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout L, Counters* __restrict__ ctr,
+                 u64 pos_lo, u64 pos_hi) {
     const u64 n = ctr->n_survived;
     const u32 ks = L.key_shift();
     const u32 lane = threadIdx.x & 31;
@@ -252,8 +256,8 @@ diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout
                 const bool head = (p >> ks) != (cur >> ks);
                 const bool emit = rec_type(cur) == kTypeDeleted || head || rec_type(p) == kTypeDeleted ||
                                   eff_phase(rec_phase(p)) != eff_phase(rec_phase(cur));
-                if (emit) {
-                    const u64 pos = rec_idx(L, cur);
+                const u64 pos = rec_idx(L, cur);
+                if (emit && pos >= pos_lo && pos < pos_hi) {
                     atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
                     tomb += rec_type(cur) == kTypeDeleted;
                 }
@@ -268,25 +272,41 @@ diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout
 // ---- payload columns --------------------------------------------------------
 // Emitted records -> the columns a sink needs (idx, rv, key, ns_id, phase, type), in replay order.
 struct AssembleArgs {
-    const u64* rec;        // arrival-ordered records (rec_out of intern_pack_kernel)
     const u32* origin;     // compacted position -> arrival index (NULL: identity)
     const u32* bitmap;     // emit bit per position (bitmap kernel only)
-    const u64* rv; const u32* ns;
-    RecLayout L;
+    const u64* rv; const u32* ns; const u8* phase; const u8* type;   // the log
     Counters* ctr;
     u32* lookback;
-    u32* out_idx; u64* out_rv; u64* out_key; u32* out_ns; u8* out_phase; u8* out_type;
+    u32* out_idx; u64* out_rv; u32* out_ns; u8* out_phase; u8* out_type;
 };
 
+// The interned key is not written here: few sinks want it, and pte_fetch can look it up on demand.
 __device__ __forceinline__ void assemble_one(const AssembleArgs& a, u64 pos, u64 j) {
-    const u64 r = a.rec[pos];
     const u32 idx = a.origin ? a.origin[pos] : (u32)pos;
     a.out_idx[j] = idx;
-    a.out_rv[j] = __ldg(a.rv + idx);
-    a.out_key[j] = rec_key(a.L, r);
-    a.out_ns[j] = __ldg(a.ns + idx);
-    a.out_phase[j] = (u8)rec_phase(r);
-    a.out_type[j] = (u8)rec_type(r);
+    a.out_rv[j] = __ldcs(a.rv + idx);
+    a.out_ns[j] = __ldcs(a.ns + idx);
+    a.out_phase[j] = __ldcs(a.phase + idx);
+    a.out_type[j] = __ldcs(a.type + idx);
+}
+
+// Interned key of each emitted record, on demand: a read-only walk of the uid dictionary.
+__global__ void __launch_bounds__(256)
+key_lookup_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict__ uid_hi, const u64* __restrict__ uid_lo,
+                  const Slot* __restrict__ table, u32 mask, u64* __restrict__ out_key) {
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
+        const u32 i = out_idx[j];
+        const u64 hi = uid_hi[i], lo = uid_lo[i];
+        u32 sl = uid_home_slot(hi, lo, mask);
+        u64 key = ~0ull;
+        for (int p = 0; p < kMaxProbe; ++p) {
+            ulonglong2 v = *reinterpret_cast<const ulonglong2*>(table + sl);
+            if (v.x == hi && v.y == lo) { key = sl; break; }
+            if ((v.x | v.y) == 0) break;
+            sl = (sl + 1) & mask;
+        }
+        out_key[j] = key;
+    }
 }
 
 // R-trace: every survivor is emitted, position == output row.
@@ -346,7 +366,33 @@ __global__ void __launch_bounds__(256) assemble_bitmap_kernel(AssembleArgs a) {
         __syncthreads();
         const u64 tbase = (u64)tile * kAsmTile, obase = s_excl;
         const u32 cnt = s_total;
-        for (u32 j = tid; j < cnt; j += 256) assemble_one(a, tbase + s_pos[j], obase + j);
+        // four rows per thread and iteration, all gathers issued before the first store
+        for (u32 j0 = tid; j0 < cnt; j0 += 4 * 256) {
+            u32 idx[4], ns[4];
+            u64 rv[4];
+            u8 ph[4], ty[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const u32 j = j0 + k * 256;
+                if (j < cnt) {
+                    const u64 pos = tbase + s_pos[j];
+                    idx[k] = a.origin ? a.origin[pos] : (u32)pos;
+                    rv[k] = __ldcs(a.rv + idx[k]);
+                    ns[k] = __ldcs(a.ns + idx[k]);
+                    ph[k] = __ldcs(a.phase + idx[k]);
+                    ty[k] = __ldcs(a.type + idx[k]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const u32 j = j0 + k * 256;
+                if (j < cnt) {
+                    const u64 o = obase + j;
+                    a.out_idx[o] = idx[k]; a.out_rv[o] = rv[k]; a.out_ns[o] = ns[k];
+                    a.out_phase[o] = ph[k]; a.out_type[o] = ty[k];
+                }
+            }
+        }
     }
 }
 
