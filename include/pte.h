@@ -163,6 +163,27 @@ uint32_t pte_shard_of(uint64_t uid_hi, uint64_t uid_lo, uint32_t n_shards);
  * kernels, in place in the caller's host array.  Test hook for the sort in isolation. */
 int pte_debug_sort_u64(pte_handle h, uint64_t* records, uint64_t n, int bit_lo, int bit_hi);
 
+/* No counterpart in the reference.
+ * One stable radix scatter pass that allocates nothing, for hosts where this library must not
+ * call cudaMalloc: servers that give all device memory to their own pool at start-up, and plug-ins
+ * on latency-critical paths that cannot take the device-wide stall an allocation may cause.
+ * out receives the n records of `in` stably partitioned by the digit in bits [bit_lo, bit_lo + n_bits)
+ * (n_bits 1..8) -- the same result as pte_debug_sort_u64 on that bit range.  in and out are distinct,
+ * caller-owned, 8-byte aligned and reachable from the GPU (device memory, or pinned host memory such as
+ * pte_host_alloc returns); no padding is needed.  The work runs on `stream` (a cudaStream_t, NULL for
+ * the default stream) of the current device and the call returns when it is done.
+ * The histogram and look-back scratch is a fixed array inside the library's device image, about 1 MB that
+ * every GPU which loads libpte.so holds until the process exits.  Hence:
+ *   - n may not exceed PTE_STATIC_MAX_RECORDS; more is refused with PTE_ERR_CAPACITY;
+ *   - all calls on one GPU share the array (each call first clears what it will read), so two calls
+ *     that overlap on the same GPU -- from two threads or two streams -- race: serialise them;
+ *   - the first call on each GPU looks up the array's device address and sets kernel attributes;
+ *     make that call before any stream capture begins.
+ * On failure the reason is copied to err (capacity err_cap) when err is not NULL. */
+#define PTE_STATIC_MAX_RECORDS (1ull << 22)
+int pte_partition_u64_static(const uint64_t* in, uint64_t* out, uint64_t n, int bit_lo, int n_bits,
+                             void* stream, char* err, size_t err_cap);
+
 /* ---- multi-GPU: one engine per process/GPU, a single collective --------- */
 
 /* NCCL bootstrap: rank 0 makes an id, the host layer ships its 128 bytes to every rank. */

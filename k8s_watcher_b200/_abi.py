@@ -63,6 +63,7 @@ SYMBOLS = {
     "pte_host_free": (None, [C.c_void_p]),
     "pte_shard_of": (C.c_uint32, [C.c_uint64, C.c_uint64, C.c_uint32]),
     "pte_debug_sort_u64": (C.c_int, [C.c_void_p, _u64p, C.c_uint64, C.c_int, C.c_int]),
+    "pte_partition_u64_static": (C.c_int, [_u64p, _u64p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_char_p, C.c_size_t]),
     "pte_comm_unique_id": (C.c_int, [C.c_char_p]),
     "pte_comm_init": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int]),
     "pte_gather_counts": (C.c_int, [C.c_void_p, _u64p]),

@@ -48,6 +48,25 @@ def shard_of(uid_hi: int, uid_lo: int, n_shards: int) -> int:
     return int(_abi.lib().pte_shard_of(int(uid_hi), int(uid_lo), int(n_shards)))
 
 
+STATIC_MAX_RECORDS = 1 << 22
+
+
+def partition_u64_static(src: np.ndarray, dst: np.ndarray, bit_lo: int, n_bits: int, stream: int = 0) -> None:
+    """pte_partition_u64_static: one stable radix pass that allocates nothing on the device.
+
+    For hosts that own all device memory themselves and forbid library allocations.  ``src`` and ``dst``
+    must be GPU-reachable uint64 arrays of the same length (e.g. ``PinnedBuffer(...).array``); at most
+    ``STATIC_MAX_RECORDS`` records; calls on one GPU must not overlap (they share one scratch array).
+    """
+    if src.dtype != np.uint64 or dst.dtype != np.uint64 or src.shape != dst.shape or src.ndim != 1:
+        raise ValueError("src and dst must be 1-d uint64 arrays of equal length")
+    err = C.create_string_buffer(256)
+    rc = _abi.lib().pte_partition_u64_static(_ptr(src, C.c_uint64), _ptr(dst, C.c_uint64), int(src.shape[0]),
+                                             int(bit_lo), int(n_bits), C.c_void_p(stream), err, 256)
+    if rc != _abi.PTE_OK:
+        raise PteError(rc, err.value.decode(errors="replace"))
+
+
 class PinnedBuffer:
     """Page-locked host array (pte_host_alloc) viewed through numpy."""
 
