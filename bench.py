@@ -201,12 +201,8 @@ def main():
     from k8s_watcher_b200 import PhaseTransitionEngine
     from k8s_watcher_b200.engine import PinnedBuffer
 
-    dist_t = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_t
-        torch.cuda.set_device(local)
-        dist_t.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from k8s_watcher_b200 import sharding
+    dist_t = sharding.init_process_group("nccl", local) if world > 1 else None
 
     def barrier():
         if dist_t is not None:
@@ -214,9 +210,8 @@ def main():
 
     eng = PhaseTransitionEngine(ev, pods, device=local)
     if world > 1:
-        ids = [PhaseTransitionEngine.comm_unique_id() if rank == 0 else None]
-        dist_t.broadcast_object_list(ids, src=0)
-        eng.comm_init(ids[0], rank, world)
+        uid = sharding.broadcast_bytes(dist_t, PhaseTransitionEngine.comm_unique_id() if rank == 0 else None)
+        eng.comm_init(uid, rank, world)
     eng.set_filters(None)                                   # staging regime: every event reaches the sort
     eng.generate(SEED, ev, pods, dist=dist, p_del=p_del, shard=rank, n_shards=world)
 
@@ -247,10 +242,7 @@ def main():
 
     step_ms = (dev_ms + gather_ms) / args.steps
     if world > 1:
-        import torch
-        t = torch.tensor([step_ms, wall_ms / args.steps], device="cuda", dtype=torch.float64)
-        dist_t.all_reduce(t, op=dist_t.ReduceOp.MAX)
-        step_ms, wall_step_ms = float(t[0]), float(t[1])
+        step_ms, wall_step_ms = sharding.max_over_ranks(dist_t, [step_ms, wall_ms / args.steps])
         total_events = int(counts[:, 0].sum())
         total_emitted = int(counts[:, 2].sum())
     else:
@@ -276,14 +268,10 @@ def main():
     if not args.no_e2e:
         e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier)
         if world > 1:
-            import torch
-            t = torch.tensor([e2e["ms_per_step"]], device="cuda", dtype=torch.float64)
-            dist_t.all_reduce(t, op=dist_t.ReduceOp.MAX)
-            e2e["ms_per_step"] = float(t[0])
-            b = torch.tensor([e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"]], device="cuda", dtype=torch.float64)
-            dist_t.all_reduce(b)
-            e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"] = int(b[0]), int(b[1])
-        e2e["value"] = total_events / (e2e["ms_per_step"] * 1e-3)
+            e2e["ms_per_step"] = sharding.max_over_ranks(dist_t, [e2e["ms_per_step"]])[0]
+            b = sharding.gather_counts_pg(dist_t, [e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"], 0, 0])
+            e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"] = int(b[:, 0].sum()), int(b[:, 1].sum())
+        e2e["value"] = sharding.throughput(total_events, e2e["ms_per_step"])
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -291,7 +279,7 @@ def main():
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": total_events / (step_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "metric": METRIC, "value": sharding.throughput(total_events, step_ms), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": {"workload": desc, "events_per_gpu": ev, "pods_per_gpu": pods, "filters": "staging (none)",

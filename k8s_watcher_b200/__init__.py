@@ -8,6 +8,7 @@ from .clusterapi_client import ClusterApiClient, MockTransport  # noqa: F401
 from .engine import EmittedColumns, PhaseTransitionEngine, PteError, generate_host, shard_of  # noqa: F401
 from .pod_watcher import Batch, PodWatcher  # noqa: F401
 from .replay_log import ReplayLog  # noqa: F401
+from . import sharding  # noqa: F401
 
 __all__ = ["PodWatcher", "Batch", "ClusterApiClient", "MockTransport", "PhaseTransitionEngine", "EmittedColumns",
            "ReplayLog", "PteError", "generate_host", "shard_of"]
