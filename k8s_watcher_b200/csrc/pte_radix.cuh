@@ -94,13 +94,40 @@ struct RadixPassSmem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
     u64 stage[TILE];
-    u32 warp_hist[WARPS][kRadix];
+    u32 warp_hist[WARPS][kRadix];   // per warp: digit counts, then running offsets inside the tile
     u32 bin_base[kRadix];
-    u32 tile_excl[kRadix];
     u32 dst_off[kRadix];
     u32 tot[8];
     u32 tile;
 };
+
+// One digit of one warp-wide step: lanes holding the same digit find each other with one ballot per
+// digit bit (MATCH.ANY would do it in one instruction but runs on the ADU pipe at 62 cycles per warp
+// instruction, which then bounds the whole pass -- profiles/), the first of them advances the warp's
+// running offset for that digit, and every lane gets its place in tile order.
+template <bool CHECK_VALID>
+__device__ __forceinline__ u32 rank_in_warp(u32* __restrict__ warp_off, u32 d, bool valid, u32 lt) {
+    u32 peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const u32 m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    if (CHECK_VALID) {
+        const u32 vm = __ballot_sync(0xffffffffu, valid);
+        peers &= valid ? vm : ~vm;
+    }
+    const u32 before = peers & lt;
+    u32 base = 0;
+    if (before == 0 && valid) {
+        base = warp_off[d];
+        warp_off[d] = base + __popc(peers);
+    }
+    __syncwarp();
+    base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
+    return base + __popc(before);
+}
 
 template <int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? 4 : 2))
@@ -128,87 +155,84 @@ radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* 
         const u64 tile_base = (u64)tile * TILE;
         if (tile_base >= n) break;
         const u32 tile_valid = (u32)min((u64)TILE, n - tile_base);
+        const bool full_tile = tile_valid == TILE;
 
         // (1) warp-striped load: warp w owns records [w*32*ITEMS, (w+1)*32*ITEMS) of the tile
         u64 key[ITEMS];
-        u32 rank[ITEMS];
         const u32 wbase = warp * 32 * ITEMS + lane;
 #pragma unroll
         for (int k = 0; k < ITEMS; k++) {
             u32 t = wbase + k * 32;
             key[k] = t < tile_valid ? __ldcs(in + tile_base + t) : ~0ull;
         }
-        // (2) rank inside the warp, in record order, against the warp's private digit counters.
-        // Peers (lanes holding the same digit) come from one ballot per digit bit: MATCH.ANY would do
-        // it in one instruction but runs on the ADU pipe, which then bounds the whole pass (profiles/).
-        const bool full_tile = tile_valid == TILE;
+        // (2) early counts: a cheap pass of shared-memory reductions, so that the tile's digit counts
+        // reach the look-back chain long before the expensive ranking is done
 #pragma unroll
-        for (int k = 0; k < ITEMS; k++) {
-            const bool valid = full_tile || wbase + k * 32 < tile_valid;
-            const u32 d = (u32)(key[k] >> shift) & mask;
-            u32 peers = 0xffffffffu;
-#pragma unroll
-            for (int b = 0; b < 8; b++) {
-                const bool bit = (d >> b) & 1u;
-                const u32 m = __ballot_sync(0xffffffffu, bit);
-                peers &= bit ? m : ~m;
-            }
-            if (!full_tile) {
-                const u32 vm = __ballot_sync(0xffffffffu, valid);
-                peers &= valid ? vm : ~vm;
-            }
-            const u32 before = peers & lt;
-            u32 base = 0;
-            if (before == 0 && valid) {
-                base = s.warp_hist[warp][d];
-                s.warp_hist[warp][d] = base + __popc(peers);
-            }
-            __syncwarp();
-            base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
-            rank[k] = base + __popc(before);
-        }
+        for (int k = 0; k < ITEMS; k++)
+            if (full_tile || wbase + k * 32 < tile_valid) atomicAdd(&s.warp_hist[warp][(u32)(key[k] >> shift) & mask], 1u);
         __syncthreads();
 
-        // (3) per digit: counts of this tile, offsets of each warp inside the digit, publish the partial
-        u32 count = 0;
+        // (3) per digit: tile count (published at once), each warp's start inside the tile
+        u32 count = 0, tile_excl = 0;
         if (tid < kRadix) {
             u32 run = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) run += s.warp_hist[w][tid];
+            count = run;
+            st_relaxed_u32(lookback + (u64)tile * kRadix + tid, (tile == 0 ? kLbInclusive : kLbPartial) | count);
+            tile_excl = excl_scan_256(count, s.tot, nullptr);
+            run = tile_excl;
 #pragma unroll
             for (int w = 0; w < WARPS; w++) {
                 u32 t = s.warp_hist[w][tid];
                 s.warp_hist[w][tid] = run;
                 run += t;
             }
-            count = run;
-            st_relaxed_u32(lookback + (u64)tile * kRadix + tid, (tile == 0 ? kLbInclusive : kLbPartial) | count);
-            s.tile_excl[tid] = excl_scan_256(count, s.tot, nullptr);
         }
         __syncthreads();
 
-        // (4) re-order the tile in shared memory
+        // (4) rank inside the warp, in record order, and drop every record at its place in tile order
+        if (full_tile) {
 #pragma unroll
-        for (int k = 0; k < ITEMS; k++) {
-            if (wbase + k * 32 < tile_valid) {
-                const u32 d = (u32)(key[k] >> shift) & mask;
-                s.stage[s.tile_excl[d] + s.warp_hist[warp][d] + rank[k]] = key[k];
+            for (int k = 0; k < ITEMS; k++) {
+                const u32 pos = rank_in_warp<false>(s.warp_hist[warp], (u32)(key[k] >> shift) & mask, true, lt);
+                s.stage[pos] = key[k];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < ITEMS; k++) {
+                const bool valid = wbase + k * 32 < tile_valid;
+                const u32 pos = rank_in_warp<true>(s.warp_hist[warp], (u32)(key[k] >> shift) & mask, valid, lt);
+                if (valid) s.stage[pos] = key[k];
             }
         }
 
-        // (5) decoupled look-back: records of this digit in all earlier tiles
+        // (5) decoupled look-back: records of this digit in all earlier tiles.  Four predecessors are
+        // read per step so that the walk costs one L2 round trip per four tiles.
         if (tid < kRadix) {
             u32 excl = 0;
             if (tile > 0) {
-                u32 t = tile - 1;
-                for (;;) {
-                    u32 v = ld_relaxed_u32(lookback + (u64)t * kRadix + tid);
-                    if ((v >> 30) == 0) { __nanosleep(20); continue; }
-                    excl += v & kLbValue;
-                    if ((v >> 30) == 2) break;
-                    t--;
+                int t = (int)tile - 1;
+                bool done = false;
+                while (!done) {
+                    u32 v[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        v[j] = t - j >= 0 ? ld_relaxed_u32(lookback + (u64)(t - j) * kRadix + tid) : kLbInclusive;
+                    int used = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (done || (v[j] >> 30) == 0) break;
+                        excl += v[j] & kLbValue;
+                        used++;
+                        if ((v[j] >> 30) == 2) done = true;
+                    }
+                    t -= used;
+                    if (!done && used == 0) __nanosleep(40);
                 }
                 st_relaxed_u32(lookback + (u64)tile * kRadix + tid, kLbInclusive | (excl + count));
             }
-            s.dst_off[tid] = s.bin_base[tid] + excl - s.tile_excl[tid];
+            s.dst_off[tid] = s.bin_base[tid] + excl - tile_excl;
         }
         __syncthreads();
 
