@@ -25,23 +25,23 @@ inline u64 round_up(u64 x, u64 m) { return (x + m - 1) / m * m; }
 inline u32 bitlen_host(u64 x) { u32 n = 0; while (x) { n++; x >>= 1; } return n; }
 
 // radix pass configurations (threads, records per thread); PTE_PASS_CFG picks one for tuning runs
-struct PassCfg { int threads, items; };
-constexpr PassCfg kPassCfgs[] = {{256, 16}, {512, 8}, {384, 12}, {256, 8}, {512, 12}};
+struct PassCfg { int threads, items, ballot_items; };
+constexpr PassCfg kPassCfgs[] = {{384, 16, 0}, {512, 12, 0}, {512, 12, 4}, {512, 12, 12}, {256, 16, 0}, {512, 16, 0}};
 constexpr int kNumPassCfgs = sizeof(kPassCfgs) / sizeof(kPassCfgs[0]);
 
-template <int T, int I>
+template <int T, int I, int B>
 cudaError_t launch_pass(int grid, cudaStream_t st, const u64* in, u64* out, const u64* n_ptr, u64 n_fixed, int shift,
                         u32 mask, const u32* hist, u32* lookback, u32* ticket) {
     size_t smem = sizeof(RadixPassSmem<T, I>);
-    radix_pass_kernel<T, I><<<grid, T, smem, st>>>(in, out, n_ptr, n_fixed, shift, mask, hist, lookback, ticket);
+    radix_pass_kernel<T, I, B><<<grid, T, smem, st>>>(in, out, n_ptr, n_fixed, shift, mask, hist, lookback, ticket);
     return cudaGetLastError();
 }
-template <int T, int I>
+template <int T, int I, int B>
 cudaError_t prepare_pass(int* occ) {
     size_t smem = sizeof(RadixPassSmem<T, I>);
-    cudaError_t e = cudaFuncSetAttribute(radix_pass_kernel<T, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(radix_pass_kernel<T, I, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, radix_pass_kernel<T, I>, T, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, radix_pass_kernel<T, I, B>, T, smem);
 }
 
 struct NcclApi {
@@ -89,7 +89,7 @@ struct pte_engine {
     u32 *origin = nullptr, *bitmap = nullptr;                // compacted position -> arrival index; emit bits
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
-    int pass_cfg = 4, pass_occ = 1, pass_tile = 6144;
+    int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
     u64 diff_round_bytes = 64ull << 20;      // bitmap bytes one diff round may touch
     bool key_valid = false;                  // out_key holds the keys of the last run
     Counters* ctr = nullptr;
@@ -131,17 +131,18 @@ struct pte_engine {
 
 namespace {
 
+#define PTE_FOR_EACH_PASS_CFG(X) \
+    X(0, 384, 16, 0) X(1, 512, 12, 0) X(2, 512, 12, 4) X(3, 512, 12, 12) X(4, 256, 16, 0) X(5, 512, 16, 0)
+
 int launch_pass_cfg(pte_engine* h, const u64* in, u64* out, const u64* n_ptr, u64 n_fixed, int shift, u32 mask,
                     const u32* hist) {
     int grid = h->num_sms * h->pass_occ;
     u32* ticket = &h->ctr->ticket[1];
-    cudaError_t e;
+    cudaError_t e = cudaErrorInvalidValue;
     switch (h->pass_cfg) {
-        case 1: e = launch_pass<512, 8>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
-        case 2: e = launch_pass<384, 12>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
-        case 3: e = launch_pass<256, 8>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
-        case 4: e = launch_pass<512, 12>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
-        default: e = launch_pass<256, 16>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+#define X(id, T, I, B) case id: e = launch_pass<T, I, B>(grid, h->stream, in, out, n_ptr, n_fixed, shift, mask, hist, h->lookback, ticket); break;
+        PTE_FOR_EACH_PASS_CFG(X)
+#undef X
     }
     if (e != cudaSuccess) FAIL(h, PTE_ERR_CUDA, std::string("radix_pass_kernel: ") + cudaGetErrorString(e));
     h->n_launches++;
@@ -149,13 +150,11 @@ int launch_pass_cfg(pte_engine* h, const u64* in, u64* out, const u64* n_ptr, u6
 }
 
 int prepare_pass_cfg(pte_engine* h) {
-    cudaError_t e;
+    cudaError_t e = cudaErrorInvalidValue;
     switch (h->pass_cfg) {
-        case 1: e = prepare_pass<512, 8>(&h->pass_occ); break;
-        case 2: e = prepare_pass<384, 12>(&h->pass_occ); break;
-        case 3: e = prepare_pass<256, 8>(&h->pass_occ); break;
-        case 4: e = prepare_pass<512, 12>(&h->pass_occ); break;
-        default: e = prepare_pass<256, 16>(&h->pass_occ); break;
+#define X(id, T, I, B) case id: e = prepare_pass<T, I, B>(&h->pass_occ); break;
+        PTE_FOR_EACH_PASS_CFG(X)
+#undef X
     }
     if (e != cudaSuccess) FAIL(h, PTE_ERR_CUDA, std::string("radix pass set-up: ") + cudaGetErrorString(e));
     if (h->pass_occ < 1) FAIL(h, PTE_ERR_CUDA, "radix pass does not fit on an SM");
@@ -168,16 +167,18 @@ int prepare_pass_cfg(pte_engine* h) {
 // n is read on the device from n_ptr when given (n_upper bounds it for sizing), else n_upper.
 // On return *result points at the buffer that holds the sorted records.
 int sort_field(pte_engine* h, u64* src, u64* x, u64* y, const u64* n_ptr, u64 n_upper, int bit_lo, int bit_hi,
-               u64** result) {
+               u64** result, bool hist_ready = false) {
     *result = src;
     if (bit_hi <= bit_lo || n_upper == 0) return PTE_OK;
     const int passes = (bit_hi - bit_lo + 7) / 8;
     if (passes > kMaxPasses) FAIL(h, PTE_ERR_INVALID, "sort field wider than 64 bits");
-    CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, h->stream));
-    int hgrid = (int)std::min<u64>((u64)h->num_sms * 8, (n_upper + 511) / 512);
-    radix_hist_kernel<256><<<std::max(hgrid, 1), 256, 0, h->stream>>>(src, n_ptr, n_upper, bit_lo, passes, bit_hi, h->hist);
-    CK(h, cudaGetLastError());
-    h->n_launches++;
+    if (!hist_ready) {     // the producer of the records may have counted the digits already
+        CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, h->stream));
+        int hgrid = (int)std::min<u64>((u64)h->num_sms * 8, (n_upper + 511) / 512);
+        radix_hist_kernel<256><<<std::max(hgrid, 1), 256, 0, h->stream>>>(src, n_ptr, n_upper, bit_lo, passes, bit_hi, h->hist);
+        CK(h, cudaGetLastError());
+        h->n_launches++;
+    }
     const u64 tiles = (n_upper + h->pass_tile - 1) / h->pass_tile;
     if (tiles * kRadix > h->lookback_words) FAIL(h, PTE_ERR_CAPACITY, "look-back buffer too small");
     u64 *a = src, *b = x;
@@ -468,6 +469,8 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         a.origin = h->origin;
         a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
         a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
+        a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
+        CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, st));
         const u64 tiles = (n + kInternTile - 1) / kInternTile;
         int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
         if (filtered) {
@@ -489,7 +492,7 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     if (n && dedupe) {
         u64* sorted = nullptr;
         int rc = sort_field(h, h->recA, h->recB, h->recC, &h->ctr->n_survived, n, h->L.key_shift(),
-                            h->L.key_shift() + h->L.key_bits, &sorted);
+                            h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[2], st));
         CK(h, cudaMemsetAsync(h->bitmap, 0, ((n + 31) / 32) * sizeof(u32), st));

@@ -80,6 +80,8 @@ struct InternArgs {
     const u32* ns_bitmap; u32 ns_words; int ns_filter_on; int critical_only;
     Counters* ctr;
     u32* lookback;     // one word per tile (FILTERED only)
+    u32* hist;         // digit counts of the key field for the radix passes that follow
+    int key_passes;    // number of 8-bit digits in the key field (<= 4)
 };
 
 static constexpr int kInternThreads = 256;
@@ -95,9 +97,12 @@ template <bool FILTERED>
 __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs a) {
     __shared__ u32 s_tot[8];
     __shared__ u32 s_tile, s_tile_excl;
+    __shared__ u32 s_hist[4 * kRadix];     // the sort's digit counts are taken here: no extra read of the records
     const u32 tid = threadIdx.x, lane = tid & 31;
     u32 inserted = 0, del_surv = 0, flags = 0;
     if (!FILTERED && blockIdx.x == 0 && tid == 0) a.ctr->n_survived = a.n;
+    for (int k = tid; k < 4 * kRadix; k += kInternThreads) s_hist[k] = 0;
+    __syncthreads();
     const u32 n_tiles = (u32)((a.n + kInternTile - 1) / kInternTile);
 
     for (u32 tile = blockIdx.x;; tile += gridDim.x) {
@@ -203,6 +208,9 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
                 const u64 pos = FILTERED ? dst : i0 + k;
                 rec[k] = rec_pack(a.L, slot, pos, ty[k], ph[k]);
                 del_surv += ty[k] == kTypeDeleted;
+#pragma unroll
+                for (int p = 0; p < 4; p++)
+                    if (p < a.key_passes) atomicAdd(&s_hist[p * kRadix + ((slot >> (8 * p)) & 0xFF)], 1u);
                 if (FILTERED) { a.rec_out[dst] = rec[k]; a.origin[dst] = (u32)(i0 + k); dst++; }
             }
         }
@@ -213,6 +221,9 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
             __stcs(o + 1, make_ulonglong2(rec[2], rec[3]));
         }
     }
+    __syncthreads();
+    for (int k = tid; k < a.key_passes * kRadix; k += kInternThreads)
+        if (s_hist[k]) atomicAdd(&a.hist[k], s_hist[k]);
     // one atomic per warp for the run-wide counters
     inserted = __reduce_add_sync(0xffffffffu, inserted);
     del_surv = __reduce_add_sync(0xffffffffu, del_surv);

@@ -3,7 +3,7 @@
 //   radix_hist_kernel  one read of the records -> digit counts of every pass
 //   radix_pass_kernel  one scatter pass: read 8 B, write 8 B per record, single sweep.
 //                      Tiles are chained with a decoupled look-back over per-tile digit
-//                      counts, digits are ranked inside a warp with ballot-built peer masks + popc
+//                      counts, digits are ranked inside a warp with peer masks built by shared-memory atomicOr + popc
 //                      (stable: lower lanes first), and every tile is re-ordered in shared
 //                      memory first so that global writes are runs of consecutive records.
 //
@@ -95,18 +95,24 @@ struct RadixPassSmem {
     static constexpr int TILE = THREADS * ITEMS;
     u64 stage[TILE];
     u32 warp_hist[WARPS][kRadix];   // per warp: digit counts, then running offsets inside the tile
+    u32 peer_mask[WARPS][kRadix];   // per warp and digit: lanes of the step in flight holding that digit (0 between steps)
     u32 bin_base[kRadix];
     u32 dst_off[kRadix];
     u32 tot[8];
-    u32 tile;
+    u32 tile, next_tile;
 };
 
-// One digit of one warp-wide step: lanes holding the same digit find each other with one ballot per
-// digit bit (MATCH.ANY would do it in one instruction but runs on the ADU pipe at 62 cycles per warp
-// instruction, which then bounds the whole pass -- profiles/), the first of them advances the warp's
-// running offset for that digit, and every lane gets its place in tile order.
+// One digit of one warp-wide step.  Lanes holding the same digit have to find each other (stable
+// ranking: lower lanes first); the first of them then advances the warp's running offset for the
+// digit.  Three ways to get the peer mask on sm_100a (tools/ubench.cu, profiles/):
+//   MATCH.ANY        one instruction, but 62 cycles per warp instruction per SM on the ADU pipe;
+//   eight ballots    ~22 cycles of the vote path plus ~40 ALU-pipe instructions;
+//   shared atomicOr  every lane ORs its lane bit into the warp's mask word of its digit and reads the
+//                    word back: under 3 cycles per op, but ~3.4 bank-conflict wavefronts each.
+// The pass mixes the last two (BALLOT_ITEMS of a thread's records use ballots, the rest atomics) so
+// that neither the ALU pipe nor the shared-memory pipe is the only one busy.
 template <bool CHECK_VALID>
-__device__ __forceinline__ u32 rank_in_warp(u32* __restrict__ warp_off, u32 d, bool valid, u32 lt) {
+__device__ __forceinline__ u32 rank_by_ballot(u32* __restrict__ warp_off, u32 d, bool valid, u32 lt) {
     u32 peers = 0xffffffffu;
 #pragma unroll
     for (int b = 0; b < 8; b++) {
@@ -120,17 +126,32 @@ __device__ __forceinline__ u32 rank_in_warp(u32* __restrict__ warp_off, u32 d, b
     }
     const u32 before = peers & lt;
     u32 base = 0;
-    if (before == 0 && valid) {
-        base = warp_off[d];
-        warp_off[d] = base + __popc(peers);
-    }
-    __syncwarp();
-    base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
+    if (before == 0 && (!CHECK_VALID || valid)) base = atomicAdd(warp_off + d, (u32)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, (__ffs(peers) - 1) & 31);
     return base + __popc(before);
 }
 
-template <int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? 4 : 2))
+template <bool CHECK_VALID>
+__device__ __forceinline__ u32 rank_by_atomic(u32* __restrict__ warp_off, u32* __restrict__ peer_mask, u32 d, bool valid,
+                                              u32 lt, u32 lane_bit) {
+    const bool on = !CHECK_VALID || valid;
+    if (on) atomicOr(peer_mask + d, lane_bit);
+    __syncwarp();
+    const u32 peers = on ? peer_mask[d] : 0u;     // __syncwarp orders it after every peer's atomicOr
+    __syncwarp();
+    const u32 before = peers & lt;
+    u32 base = 0;
+    if (before == 0 && on) {
+        base = atomicAdd(warp_off + d, (u32)__popc(peers));
+        peer_mask[d] = 0;
+    }
+    __syncwarp();
+    base = __shfl_sync(0xffffffffu, base, (__ffs(peers) - 1) & 31);
+    return base + __popc(before);
+}
+
+template <int THREADS, int ITEMS, int BALLOT_ITEMS = 0>
+__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? 4 : (THREADS <= 512 ? 2 : 1)))
 radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ n_ptr, u64 n_fixed,
                   int shift, u32 mask, const u32* __restrict__ hist, u32* __restrict__ lookback,
                   u32* __restrict__ ticket) {
@@ -142,34 +163,44 @@ radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* 
 
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 lt = lanemask_lt();
+    const u32 lane_bit = 1u << lane;
     const u64 n = n_ptr ? *n_ptr : n_fixed;
+    const u32 wbase = warp * 32 * ITEMS + lane;
 
     if (tid < kRadix) s.bin_base[tid] = excl_scan_256(hist[tid], s.tot, nullptr);
+    for (int k = tid; k < WARPS * kRadix; k += THREADS) (&s.peer_mask[0][0])[k] = 0;
+    if (tid == 0) s.tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+
+    // warp-striped load: warp w owns records [w*32*ITEMS, (w+1)*32*ITEMS) of its tile.  The registers are
+    // free again as soon as a tile's records sit in shared memory, so the NEXT tile is loaded right then
+    // and its DRAM latency hides behind this tile's look-back and write-out.
+    u64 key[ITEMS];
+    u32 tile = s.tile;
+    auto load_tile = [&](u32 t) {
+        const u64 base = (u64)t * TILE;
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            const u64 i = base + wbase + k * 32;
+            key[k] = i < n ? __ldcs(in + i) : ~0ull;
+        }
+    };
+    load_tile(tile);
 
     for (;;) {
-        __syncthreads();   // previous tile fully written out; bin_base visible
-        if (tid == 0) s.tile = atomicAdd(ticket, 1u);
-        for (int k = tid; k < WARPS * kRadix; k += THREADS) (&s.warp_hist[0][0])[k] = 0;
-        __syncthreads();
-        const u32 tile = s.tile;
         const u64 tile_base = (u64)tile * TILE;
         if (tile_base >= n) break;
         const u32 tile_valid = (u32)min((u64)TILE, n - tile_base);
         const bool full_tile = tile_valid == TILE;
+        for (int k = tid; k < WARPS * kRadix; k += THREADS) (&s.warp_hist[0][0])[k] = 0;
+        __syncthreads();   // counters cleared; previous tile fully written out of `stage`
 
-        // (1) warp-striped load: warp w owns records [w*32*ITEMS, (w+1)*32*ITEMS) of the tile
-        u64 key[ITEMS];
-        const u32 wbase = warp * 32 * ITEMS + lane;
-#pragma unroll
-        for (int k = 0; k < ITEMS; k++) {
-            u32 t = wbase + k * 32;
-            key[k] = t < tile_valid ? __ldcs(in + tile_base + t) : ~0ull;
-        }
         // (2) early counts: a cheap pass of shared-memory reductions, so that the tile's digit counts
-        // reach the look-back chain long before the expensive ranking is done
+        // reach the look-back chain long before the ranking is done
 #pragma unroll
         for (int k = 0; k < ITEMS; k++)
             if (full_tile || wbase + k * 32 < tile_valid) atomicAdd(&s.warp_hist[warp][(u32)(key[k] >> shift) & mask], 1u);
+        if (tid == 0) s.next_tile = atomicAdd(ticket, 1u);
         __syncthreads();
 
         // (3) per digit: tile count (published at once), each warp's start inside the tile
@@ -190,22 +221,28 @@ radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* 
             }
         }
         __syncthreads();
+        const u32 next_tile = s.next_tile;
 
         // (4) rank inside the warp, in record order, and drop every record at its place in tile order
         if (full_tile) {
 #pragma unroll
             for (int k = 0; k < ITEMS; k++) {
-                const u32 pos = rank_in_warp<false>(s.warp_hist[warp], (u32)(key[k] >> shift) & mask, true, lt);
+                const u32 d = (u32)(key[k] >> shift) & mask;
+                const u32 pos = k < BALLOT_ITEMS ? rank_by_ballot<false>(s.warp_hist[warp], d, true, lt)
+                                                 : rank_by_atomic<false>(s.warp_hist[warp], s.peer_mask[warp], d, true, lt, lane_bit);
                 s.stage[pos] = key[k];
             }
         } else {
 #pragma unroll
             for (int k = 0; k < ITEMS; k++) {
                 const bool valid = wbase + k * 32 < tile_valid;
-                const u32 pos = rank_in_warp<true>(s.warp_hist[warp], (u32)(key[k] >> shift) & mask, valid, lt);
+                const u32 d = (u32)(key[k] >> shift) & mask;
+                const u32 pos = k < BALLOT_ITEMS ? rank_by_ballot<true>(s.warp_hist[warp], d, valid, lt)
+                                                 : rank_by_atomic<true>(s.warp_hist[warp], s.peer_mask[warp], d, valid, lt, lane_bit);
                 if (valid) s.stage[pos] = key[k];
             }
         }
+        load_tile(next_tile);      // in flight during (5) and (6)
 
         // (5) decoupled look-back: records of this digit in all earlier tiles.  Four predecessors are
         // read per step so that the walk costs one L2 round trip per four tiles.
@@ -245,5 +282,6 @@ radix_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* 
                 out[s.dst_off[(u32)(v >> shift) & mask] + i] = v;
             }
         }
+        tile = next_tile;
     }
 }
