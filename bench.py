@@ -229,12 +229,15 @@ def main():
     barrier()
     dev_ms = gather_ms = 0.0
     pass_ms = pass_n = 0.0
+    stage_sum = {k: 0.0 for k in ("ms_total", "ms_intern", "ms_sort_key", "ms_diff", "ms_assemble")}
     launches = 0
     wall0 = time.perf_counter()
     for _ in range(args.steps):
         st, g_ms, counts = step()
         dev_ms += st["ms_total"]; gather_ms += g_ms
         pass_ms += st["ms_pass_avg"] * st["n_passes"]; pass_n += st["n_passes"]
+        for k in stage_sum:
+            stage_sum[k] += st[k]
         launches += st["n_launches"]
     barrier()
     wall_ms = (time.perf_counter() - wall0) * 1e3
@@ -249,19 +252,38 @@ def main():
         wall_step_ms = wall_ms / args.steps
         total_events, total_emitted = int(st["n_in"]), int(st["n_emitted"])
 
-    # ---- roofline of the dominant kernel: the radix scatter pass (8 B read + 8 B written per record)
+    # ---- rooflines (all HBM-bound integer kernels).  Algorithmic bytes per launch are DESIGN.md section 3's
+    # per-event figures x the events one launch processes; durations are CUDA-event times inside pte_run.
+    peak, peak_src = _peak()
+    traffic = _traffic()
+    n_surv, n_emit, n_in = float(st["n_survived"]), float(st["n_emitted"]), float(st["n_in"])
+    avg = {k: v / args.steps for k, v in stage_sum.items()}
+    kp = int(st["n_passes"])
+    rounds = max(1, int(st["n_launches"]) - 1 - kp - 3)          # diff_flag launches
+    per_kernel = {
+        # kernel: (launches per step, algorithmic bytes per launch, ms per launch)
+        "intern_pack_kernel": (1, 30.0 * n_in + 8.0 * n_surv + 16.0 * n_surv, avg["ms_intern"]),
+        "radix_pass_kernel": (kp, 16.0 * n_surv, pass_ms / pass_n if pass_n else 0.0),
+        "diff_flag_kernel": (rounds, 8.0 * n_surv, avg["ms_diff"] / rounds),
+        "assemble_bitmap_kernel": (1, n_in / 8.0 + 14.0 * n_emit + 18.0 * n_emit, avg["ms_assemble"]),
+    }
+    by_kernel = {}
+    for name, (per_step, nbytes, ms) in per_kernel.items():
+        if ms <= 0:
+            continue
+        ach = nbytes / (ms * 1e-3) / 1e9
+        by_kernel[name] = {"launches_per_step": per_step, "avg_launch_ms": ms, "algorithmic_bytes_per_launch": nbytes,
+                           "achieved": ach, "frac": ach / peak, "share_of_step": per_step * ms / avg["ms_total"],
+                           "traffic": traffic.get(name)}
+    dom = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"]) if by_kernel else None
     roof = None
-    if pass_n:
-        # records moved per launch: key passes see n_survived records, order passes n_emitted
-        kp = _key_passes(pods)
-        op = int(st["n_passes"]) - kp
-        bytes_per_step = 16.0 * (kp * st["n_survived"] + op * st["n_emitted"])
-        peak, peak_src = _peak()
-        ach = bytes_per_step * args.steps / (pass_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "radix_pass_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "peak_source": peak_src, "traffic": _traffic(), "launches_per_step": int(st["n_passes"]),
-                "avg_launch_ms": pass_ms / pass_n, "algorithmic_bytes_per_launch": bytes_per_step / st["n_passes"],
-                "frac_of_8TBps_nominal": ach / 8000.0}
+    if dom:
+        d = by_kernel[dom]
+        roof = {"bound": "hbm", "kernel": dom, "achieved": d["achieved"], "peak": peak, "unit": "GB/s", "frac": d["frac"],
+                "peak_source": peak_src, "traffic": d["traffic"], "launches_per_step": d["launches_per_step"],
+                "avg_launch_ms": d["avg_launch_ms"], "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
+                "share_of_step": d["share_of_step"], "frac_of_8TBps_nominal": d["achieved"] / 8000.0,
+                "note": "ms of intern/diff/assemble are stage times (kernel + its memsets)", "by_kernel": by_kernel}
 
     # ---- end to end through host buffers (rank-local; max over ranks)
     e2e = None
@@ -285,7 +307,7 @@ def main():
             "config": {"workload": desc, "events_per_gpu": ev, "pods_per_gpu": pods, "filters": "staging (none)",
                        "dedupe": True, "shards": world, "l2": "inputs (30 GB log, 8 GB record buffers) far larger than the 126 MB L2",
                        "seed": hex(SEED), "emitted_total": total_emitted, "wall_ms_per_step": wall_step_ms},
-            "stage_ms": {k: st[k] for k in ("ms_intern", "ms_sort_key", "ms_diff", "ms_sort_order", "ms_assemble")},
+            "stage_ms": {k: avg[k] for k in ("ms_intern", "ms_sort_key", "ms_diff", "ms_assemble")},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
@@ -310,35 +332,36 @@ def _peak():
 
 
 def _traffic():
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any."""
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch, per kernel, from the committed ncu --set full capture."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get("radix_pass_kernel_dram_bytes_per_launch")
+            return json.load(f).get("dram_bytes_per_launch", {})
     except Exception:
-        return None
+        return {}
 
 
 def _e2e(eng, args, np, PinnedBuffer, ev, barrier):
-    """pte_ingest (pinned host columns -> HBM) + pte_run + pte_fetch (all payload columns -> pinned host)."""
+    """What PodWatcher.replay does per batch: pte_ingest (pinned host columns -> HBM) + pte_run + pte_fetch of the
+    arrival index and event type of every notification (the host still holds the log, so that is the result)."""
     dts = (("uid_hi", np.uint64), ("uid_lo", np.uint64), ("rv", np.uint64), ("ns_id", np.uint32), ("phase", np.uint8),
            ("type", np.uint8))
     pins = {k: PinnedBuffer(ev, dt) for k, dt in dts}
     host = eng.read_log(into={k: p.array for k, p in pins.items()})           # set-up, untimed
-    odts = dict(idx=np.uint32, rv=np.uint64, key=np.uint64, ns_id=np.uint32, phase=np.uint8, type=np.uint8)
+    odts = dict(idx=np.uint32, type=np.uint8)
     opins = {k: PinnedBuffer(ev, dt) for k, dt in odts.items()}
     out = {k: p.array for k, p in opins.items()}
-    eng.ingest(host); eng.run(); eng.fetch(into=out)                          # warm-up
+    eng.ingest(host); eng.run(); eng.fetch(columns=(), into=out)              # warm-up
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
         eng.ingest(host)
         st = eng.run(dedupe=True)
-        got = eng.fetch(into=out)
+        got = eng.fetch(columns=(), into=out)
     ms = (time.perf_counter() - t0) * 1e3 / args.e2e_steps
     barrier()
     res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps,
-           "h2d_bytes_per_step": 30 * ev, "d2h_bytes_per_step": 26 * len(got),
-           "api": "pte_ingest + pte_run + pte_fetch (idx, rv, key, ns_id, phase, type) with pinned host buffers"}
+           "h2d_bytes_per_step": 30 * ev, "d2h_bytes_per_step": 5 * len(got),
+           "api": "pte_ingest + pte_run + pte_fetch(idx, type) with pinned host buffers (= PodWatcher.replay)"}
     for p in list(pins.values()) + list(opins.values()):
         p.free()
     return res

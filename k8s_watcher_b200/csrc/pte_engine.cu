@@ -509,11 +509,15 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         CK(h, cudaEventRecord(h->ev[3], st));
         CK(h, cudaEventRecord(h->ev[4], st));
         const u64 tiles = (n + kAsmTile - 1) / kAsmTile;
-        CK(h, cudaMemsetAsync(h->lookback, 0, tiles * sizeof(u32), st));
+        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
+        bitmap_count_kernel<<<grid, 256, 0, st>>>(h->bitmap, h->ctr, h->lookback);
+        CK(h, cudaGetLastError());
+        tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, h->ctr);
+        CK(h, cudaGetLastError());
         grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 6);
         assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
         CK(h, cudaGetLastError());
-        h->n_launches++;
+        h->n_launches += 3;
     } else {
         // R-trace: every survivor is emitted, already in replay order
         CK(h, cudaEventRecord(h->ev[2], st));

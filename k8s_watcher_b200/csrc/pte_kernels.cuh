@@ -42,6 +42,19 @@ __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo,
 
 static constexpr int kMaxProbe = 2048;
 
+// Dictionary slots are read with an L2 evict_last hint: the log streams through L2 with evict_first
+// (ld/st .cs), so the 126 MB L2 ends up holding mostly dictionary lines without any carve-out.
+__device__ __forceinline__ u64 l2_policy_evict_last() {
+    u64 pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ ulonglong2 ld_slot(const Slot* p, u64 pol) {
+    ulonglong2 v;
+    asm volatile("ld.global.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;" : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+
 // uid -> slot of an open-addressing table (linear probing, 16-byte slots, 0:0 = empty).
 // Exact: two uids share a slot only if all 128 bits are equal.
 // A plain 16-byte load may see a slot as empty when it is not (stale line), or half-written
@@ -50,7 +63,7 @@ static constexpr int kMaxProbe = 2048;
 // `v` is the content of slot `sl` as loaded by the caller (so that a thread can have the first
 // probe of all its events in flight before it resolves any of them).
 __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u64 hi, u64 lo, u32 sl, ulonglong2 v,
-                                          u32& inserted, u32* __restrict__ flags) {
+                                          u32& inserted, u32* __restrict__ flags, u64 pol) {
     for (int p = 0; p < kMaxProbe; ++p) {
         if (v.x == 0 || v.y == 0) {
             ulonglong2 old = cas128(table + sl, 0, 0, hi, lo);
@@ -60,7 +73,7 @@ __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u6
             return sl;
         }
         sl = (sl + 1) & mask;
-        v = *reinterpret_cast<const ulonglong2*>(table + sl);
+        v = ld_slot(table + sl, pol);
     }
     atomicOr(flags, kFlagTableFull);
     return 0;
@@ -104,6 +117,7 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     for (int k = tid; k < 4 * kRadix; k += kInternThreads) s_hist[k] = 0;
     __syncthreads();
     const u32 n_tiles = (u32)((a.n + kInternTile - 1) / kInternTile);
+    const u64 pol = l2_policy_evict_last();
 
     for (u32 tile = blockIdx.x;; tile += gridDim.x) {
         if (FILTERED) {            // look-back needs tiles handed out in order
@@ -131,7 +145,7 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             sl[k] = uid_home_slot(hi[k], lo[k], a.table_mask);
-            pv[k] = *reinterpret_cast<const ulonglong2*>(a.table + sl[k]);
+            pv[k] = ld_slot(a.table + sl[k], pol);
         }
         {
             const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
@@ -204,9 +218,9 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         for (int k = 0; k < 4; k++) {
             rec[k] = 0;
             if (keep[k]) {
-                u32 slot = intern_uid(a.table, a.table_mask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags);
+                u32 slot = intern_uid(a.table, a.table_mask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
                 const u64 pos = FILTERED ? dst : i0 + k;
-                rec[k] = rec_pack(a.L, slot, pos, ty[k], ph[k]);
+                rec[k] = rec_pack(a.L, slot, pos, ty[k], eff_phase(ph[k]));   // the diff stage compares effective phases
                 del_surv += ty[k] == kTypeDeleted;
 #pragma unroll
                 for (int p = 0; p < 4; p++)
@@ -249,8 +263,11 @@ __global__ void __launch_bounds__(256)
 diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout L, Counters* __restrict__ ctr,
                  u64 pos_lo, u64 pos_hi) {
     const u64 n = ctr->n_survived;
-    const u32 ks = L.key_shift();
     const u32 lane = threadIdx.x & 31;
+    // records carry the EFFECTIVE phase, and DELETED (type 2) is the only type with bit 7 set, so
+    //   emit  <=>  key or phase differs from the predecessor, or either of the two is a DELETED
+    const u64 diff_mask = (~0ull << L.key_shift()) | 0x3Full;
+    const u64 pos_mask = L.idx_mask() << 8, lo8 = pos_lo << 8, hi8 = pos_hi << 8;
     u32 tomb = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x * 2;
     // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffle
@@ -262,18 +279,15 @@ diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout
         const u64 r[2] = {c.x, c.y};
 #pragma unroll
         for (int k = 0; k < 2; k++) {
-            if (i + k < n) {
-                const u64 cur = r[k];
-                const bool head = (p >> ks) != (cur >> ks);
-                const bool emit = rec_type(cur) == kTypeDeleted || head || rec_type(p) == kTypeDeleted ||
-                                  eff_phase(rec_phase(p)) != eff_phase(rec_phase(cur));
-                const u64 pos = rec_idx(L, cur);
-                if (emit && pos >= pos_lo && pos < pos_hi) {
-                    atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
-                    tomb += rec_type(cur) == kTypeDeleted;
-                }
-                p = cur;
+            const u64 cur = r[k];
+            const bool emit = ((((p ^ cur) & diff_mask) | ((p | cur) & 0x80ull)) != 0) && i + k < n;
+            const u64 pos8 = cur & pos_mask;
+            if (emit && pos8 >= lo8 && pos8 < hi8) {
+                const u64 pos = pos8 >> 8;
+                atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
+                tomb += (u32)(cur >> 7) & 1u;
             }
+            p = cur;
         }
     }
     tomb = __reduce_add_sync(0xffffffffu, tomb);
@@ -328,55 +342,72 @@ __global__ void __launch_bounds__(256) assemble_all_kernel(AssembleArgs a) {
 }
 
 // T-trace: stable compaction of the positions whose emit bit is set.  A tile is 256 bitmap words
-// (8192 positions), one word per thread; tile totals are chained by a decoupled look-back; the
-// tile's emitted positions are listed in shared memory so that the column writes are coalesced.
+// (8192 positions), one word per thread.  The bitmap is small (1 bit per event), so it is read twice:
+// first to count every tile and scan the counts (two tiny kernels), then by the kernel below, whose
+// tiles are independent of each other -- no look-back chain in the kernel that moves the bytes.
 static constexpr int kAsmTile = 256 * 32;
 
-__global__ void __launch_bounds__(256) assemble_bitmap_kernel(AssembleArgs a) {
-    __shared__ u32 s_pos[kAsmTile];
+__global__ void __launch_bounds__(256)
+bitmap_count_kernel(const u32* __restrict__ bitmap, const Counters* __restrict__ ctr, u32* __restrict__ tile_count) {
+    __shared__ u32 s_w[8];
+    const u64 n = ctr->n_survived;
+    const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
+    for (u32 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const u64 w = (u64)tile * 256 + threadIdx.x;
+        u32 c = w * 32 < n ? __popc(bitmap[w]) : 0u;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            u32 t = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) t += s_w[k];
+            tile_count[tile] = t;
+        }
+        __syncthreads();
+    }
+}
+
+// exclusive scan of the tile counts, in place, by one block; also the total = n_emitted
+__global__ void __launch_bounds__(1024) tile_scan_kernel(u32* __restrict__ tile_count, Counters* __restrict__ ctr) {
+    __shared__ u32 s_part[1024];
+    const u64 n = ctr->n_survived;
+    const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
+    const u32 per = (n_tiles + 1023) / 1024;
+    const u32 lo = min(n_tiles, threadIdx.x * per), hi = min(n_tiles, lo + per);
+    u32 sum = 0;
+    for (u32 t = lo; t < hi; t++) sum += tile_count[t];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u32 run = 0;
+        for (int k = 0; k < 1024; k++) { u32 v = s_part[k]; s_part[k] = run; run += v; }
+        ctr->n_emitted = run;
+    }
+    __syncthreads();
+    u32 run = s_part[threadIdx.x];
+    for (u32 t = lo; t < hi; t++) { u32 v = tile_count[t]; tile_count[t] = run; run += v; }
+}
+
+__global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a) {
+    __shared__ unsigned short s_pos[kAsmTile];
     __shared__ u32 s_tot[8];
-    __shared__ u32 s_tile, s_excl, s_total;
     const u32 tid = threadIdx.x;
     const u64 n = a.ctr->n_survived;
     const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
-    for (;;) {
-        __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket[2], 1u);
-        __syncthreads();
-        const u32 tile = s_tile;
-        if (tile >= n_tiles) break;
+    for (u32 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const u64 wbase = (u64)tile * 256 + tid;          // bitmap word of this thread
         u32 w = wbase * 32 < n ? __ldcs(a.bitmap + wbase) : 0u;
-        u32 total;
-        u32 local = excl_scan_256(__popc(w), s_tot, &total);
-        if (tid == 0) {
-            u32 excl = 0;
-            if (tile == 0) {
-                st_relaxed_u32(a.lookback, kLbInclusive | total);
-            } else {
-                st_relaxed_u32(a.lookback + tile, kLbPartial | total);
-                u32 t = tile - 1;
-                for (;;) {
-                    u32 v = ld_relaxed_u32(a.lookback + t);
-                    if ((v >> 30) == 0) { __nanosleep(20); continue; }
-                    excl += v & kLbValue;
-                    if ((v >> 30) == 2) break;
-                    t--;
-                }
-                st_relaxed_u32(a.lookback + tile, kLbInclusive | (excl + total));
-            }
-            s_excl = excl; s_total = total;
-            if (tile + 1 == n_tiles) a.ctr->n_emitted = (u64)excl + total;
-        }
+        u32 cnt;
+        u32 local = excl_scan_256(__popc(w), s_tot, &cnt);
         const u32 p0 = tid * 32;
         while (w) {
             const u32 b = __ffs(w) - 1;
             w &= w - 1;
-            s_pos[local++] = p0 + b;
+            s_pos[local++] = (unsigned short)(p0 + b);
         }
         __syncthreads();
-        const u64 tbase = (u64)tile * kAsmTile, obase = s_excl;
-        const u32 cnt = s_total;
+        const u64 tbase = (u64)tile * kAsmTile, obase = a.lookback[tile];      // tile offsets from tile_scan_kernel
         // four rows per thread and iteration, all gathers issued before the first store
         for (u32 j0 = tid; j0 < cnt; j0 += 4 * 256) {
             u32 idx[4], ns[4];
@@ -404,6 +435,7 @@ __global__ void __launch_bounds__(256) assemble_bitmap_kernel(AssembleArgs a) {
                 }
             }
         }
+        __syncthreads();      // s_pos is reused by the next tile
     }
 }
 

@@ -179,8 +179,12 @@ class PhaseTransitionEngine:
         self.last_stats = st.as_dict()
         return self.last_stats
 
-    def fetch(self, columns: Sequence[str] = ("idx", "rv", "key", "ns_id", "phase", "type"),
+    ALL_COLUMNS = ("idx", "rv", "key", "ns_id", "phase", "type")
+
+    def fetch(self, columns: Sequence[str] = ALL_COLUMNS,
               into: Optional[Dict[str, np.ndarray]] = None) -> EmittedColumns:
+        """Emitted records of the last run.  ``idx`` (arrival index) identifies a record completely for a
+        host that still holds the log; the other columns are there for sinks that do not."""
         n = int(self.last_stats["n_emitted"]) if self.last_stats else 0
         dts = dict(idx=np.uint32, rv=np.uint64, key=np.uint64, ns_id=np.uint32, phase=np.uint8, type=np.uint8)
         out = {}

@@ -224,7 +224,8 @@ class PodWatcher:
         eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
         eng.ingest(log.columns)
         stats = eng.run(dedupe=dedupe)
-        batch = Batch(self, log, eng.fetch(), stats, dedupe)
+        # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
+        batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
         self.batches.append(batch)
         return batch
 
