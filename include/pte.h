@@ -141,7 +141,7 @@ int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv,
 int pte_run(pte_handle h, int dedupe, pte_stats* out);
 
 /* Emitted records of the last pte_run, in replay order, into caller columns (any may be NULL):
- * idx = arrival index in the ingested log, key = interned 64-bit uid key.
+ * idx = arrival index in the ingested log, key = interned 64-bit uid key (dedupe runs only; ~0 otherwise).
  * Stands in for the payload hand-off at pod_watcher.py:232-236. */
 int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t* ns_id,
               uint8_t* phase, uint8_t* type, uint64_t cap, uint64_t* n_out);

@@ -85,8 +85,8 @@ struct pte_engine {
     u64 table_cap = 0;
     RecLayout L{};
     // sort
-    u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // arrival-ordered records + sort ping-pong
-    u32 *origin = nullptr, *bitmap = nullptr;                // compacted position -> arrival index; emit bits
+    u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // interned records (round-major) + sort ping-pong
+    u32* bitmap = nullptr;                                   // one emit bit per arrival position
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
     int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
@@ -237,7 +237,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->origin, h->bitmap, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv};
     for (void* b : bufs) if (b) cudaFree(b);
@@ -301,7 +301,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
     CKC(dev_alloc(h, &h->table, h->table_cap));
     CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c)); CKC(dev_alloc(h, &h->recC, c));
-    CKC(dev_alloc(h, &h->origin, c)); CKC(dev_alloc(h, &h->bitmap, c / 32));
+    CKC(dev_alloc(h, &h->bitmap, c / 32));
     // look-back words: one per (radix tile, digit); also one per intern tile
     u64 min_tile = 2048;
     h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
@@ -462,21 +462,22 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
     CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
     const bool filtered = h->critical_only || h->ns_filter_on;
-    if (n) {
-        InternArgs a;
-        a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
-        a.n = n; a.table = h->table; a.table_mask = (u32)(h->table_cap - 1); a.L = h->L; a.rec_out = h->recA;
-        a.origin = h->origin;
-        a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
-        a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
-        a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
+    InternArgs a;
+    a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
+    a.n = n; a.table = h->table; a.table_mask = (u32)(h->table_cap - 1); a.L = h->L; a.rec_out = h->recA;
+    a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
+    a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
+    a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
+    const u64* n_surv_ptr = &h->ctr->n_survived;
+    if (n && dedupe) {
         CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, st));
         const u64 tiles = (n + kInternTile - 1) / kInternTile;
-        int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
         if (filtered) {
             CK(h, cudaMemsetAsync(h->lookback, 0, tiles * sizeof(u32), st));
+            int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 4);
             intern_pack_kernel<true><<<grid, kInternThreads, 0, st>>>(a);
         } else {
+            int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
             intern_pack_kernel<false><<<grid, kInternThreads, 0, st>>>(a);
         }
         CK(h, cudaGetLastError());
@@ -484,14 +485,14 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     }
     CK(h, cudaEventRecord(h->ev[1], st));
     AssembleArgs as;
-    as.origin = filtered ? h->origin : nullptr; as.bitmap = h->bitmap;
+    as.n = n; as.bitmap = h->bitmap;
     as.rv = h->rv; as.ns = h->ns; as.phase = h->phase; as.type = h->type;
     as.ctr = h->ctr; as.lookback = h->lookback;
     as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_ns = h->out_ns;
     as.out_phase = h->out_phase; as.out_type = h->out_type;
     if (n && dedupe) {
         u64* sorted = nullptr;
-        int rc = sort_field(h, h->recA, h->recB, h->recC, &h->ctr->n_survived, n, h->L.key_shift(),
+        int rc = sort_field(h, h->recA, h->recB, h->recC, n_surv_ptr, n, h->L.key_shift(),
                             h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[2], st));
@@ -499,38 +500,36 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         int grid = (int)std::min<u64>((n + 511) / 512, (u64)h->num_sms * 16);
         // rounds: each touches a slice of the bitmap small enough to stay in L2
         const u64 bits_per_round = h->diff_round_bytes * 8;
-        const u64 rounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
-        const u64 span = round_up((n + rounds - 1) / rounds, 32);
-        for (u64 r = 0; r < rounds; r++) {
-            diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, h->bitmap, h->L, h->ctr, r * span, std::min(n, (r + 1) * span));
+        const u64 drounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
+        const u64 span = round_up((n + drounds - 1) / drounds, 32);
+        for (u64 r = 0; r < drounds; r++) {
+            diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, r * span, std::min(n, (r + 1) * span));
             CK(h, cudaGetLastError());
             h->n_launches++;
         }
-        CK(h, cudaEventRecord(h->ev[3], st));
-        CK(h, cudaEventRecord(h->ev[4], st));
+    } else {
+        // R-trace: every survivor is emitted; nothing to intern or sort
+        CK(h, cudaEventRecord(h->ev[2], st));
+        if (n) {
+            int grid = (int)std::min<u64>(((n + 31) / 32 + 255) / 256, (u64)h->num_sms * 16);
+            filter_flag_kernel<<<grid, 256, 0, st>>>(a, h->bitmap);
+            CK(h, cudaGetLastError());
+            h->n_launches++;
+        }
+    }
+    CK(h, cudaEventRecord(h->ev[3], st));
+    CK(h, cudaEventRecord(h->ev[4], st));
+    if (n) {
         const u64 tiles = (n + kAsmTile - 1) / kAsmTile;
-        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
-        bitmap_count_kernel<<<grid, 256, 0, st>>>(h->bitmap, h->ctr, h->lookback);
+        int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
+        bitmap_count_kernel<<<grid, 256, 0, st>>>(h->bitmap, n, h->lookback);
         CK(h, cudaGetLastError());
-        tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, h->ctr);
+        tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, n, h->ctr);
         CK(h, cudaGetLastError());
         grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 6);
         assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
         CK(h, cudaGetLastError());
         h->n_launches += 3;
-    } else {
-        // R-trace: every survivor is emitted, already in replay order
-        CK(h, cudaEventRecord(h->ev[2], st));
-        CK(h, cudaMemcpyAsync(&h->ctr->n_emitted, &h->ctr->n_survived, sizeof(u64), cudaMemcpyDeviceToDevice, st));
-        CK(h, cudaMemcpyAsync(&h->ctr->n_tombstones, &h->ctr->n_del_survived, sizeof(u64), cudaMemcpyDeviceToDevice, st));
-        CK(h, cudaEventRecord(h->ev[3], st));
-        CK(h, cudaEventRecord(h->ev[4], st));
-        if (n) {
-            int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
-            assemble_all_kernel<<<grid, 256, 0, st>>>(as);
-            CK(h, cudaGetLastError());
-            h->n_launches++;
-        }
     }
     CK(h, cudaEventRecord(h->ev[5], st));
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));

@@ -21,7 +21,7 @@ struct Counters {
     u64 digest;
     u32 n_pods;
     u32 flags;
-    u32 ticket[4];         // tile tickets: [0] intern, [1] radix pass (reset per pass), [2] assemble, [3] spare
+    u32 ticket[4];         // tile tickets: [0] intern (filtered runs), [1] radix pass (reset per pass), [2..3] spare
 };
 
 __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo, u64 val_hi, u64 val_lo) {
@@ -82,6 +82,31 @@ __device__ __forceinline__ u32 uid_home_slot(u64 hi, u64 lo, u32 mask) {
     return (u32)mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull)) & mask;
 }
 
+// Exclusive prefix of per-tile totals by decoupled look-back, one word per tile, walked by one warp
+// (32 predecessors per step).  Call with all 32 lanes of one warp; every lane gets the result.
+__device__ __forceinline__ u32 lookback_scalar_warp(u32* __restrict__ lb, u32 tile, u32 total, u32 lane) {
+    if (lane == 0) st_relaxed_u32(lb + tile, (tile == 0 ? kLbInclusive : kLbPartial) | total);
+    if (tile == 0) return 0;
+    u32 excl = 0;
+    int t = (int)tile - 1;
+    for (;;) {
+        const int idx = t - (int)lane;
+        const u32 v = idx >= 0 ? ld_relaxed_u32(lb + idx) : kLbInclusive;
+        const u32 not_ready = __ballot_sync(0xffffffffu, (v >> 30) == 0);
+        const u32 inclusive = __ballot_sync(0xffffffffu, (v >> 30) == 2);
+        const int first_nr = not_ready ? __ffs(not_ready) - 1 : 32;
+        const int first_in = inclusive ? __ffs(inclusive) - 1 : 32;
+        const bool done = first_in < first_nr;
+        const int last = done ? first_in : first_nr - 1;            // lanes 0..last are summed
+        excl += __reduce_add_sync(0xffffffffu, (int)lane <= last ? (v & kLbValue) : 0u);
+        if (done) break;
+        t -= first_nr;
+        if (first_nr == 0) __nanosleep(40);
+    }
+    if (lane == 0) st_relaxed_u32(lb + tile, kLbInclusive | (excl + total));
+    return excl;
+}
+
 struct InternArgs {
     const u64* uid_hi; const u64* uid_lo; const u64* rv;
     const u32* ns; const u8* phase; const u8* type;
@@ -89,10 +114,9 @@ struct InternArgs {
     Slot* table; u32 table_mask;
     RecLayout L;
     u64* rec_out;
-    u32* origin;       // FILTERED only: arrival index of the record at each compacted position
     const u32* ns_bitmap; u32 ns_words; int ns_filter_on; int critical_only;
     Counters* ctr;
-    u32* lookback;     // one word per tile (FILTERED only)
+    u32* lookback;     // one word per tile, zeroed (FILTERED only)
     u32* hist;         // digit counts of the key field for the radix passes that follow
     int key_passes;    // number of 8-bit digits in the key field (<= 4)
 };
@@ -101,11 +125,25 @@ static constexpr int kInternThreads = 256;
 static constexpr int kInternPerThread = 4;
 static constexpr int kInternTile = kInternThreads * kInternPerThread;
 
-// One event per (thread, k): thread t of a tile owns events 4t..4t+3, loaded with 16-byte vectors.
-// The record's position field is the record's place in rec_out:
-// FILTERED == false: no predicate is active, event i goes to rec_out[i].
-// FILTERED == true : survivors are compacted in arrival order (tile totals chained by look-back)
-//                    and origin[] remembers where each one came from.
+// The reference's two predicates, on integer codes.
+__device__ __forceinline__ bool passes_filters(const InternArgs& a, u32 ty, u32 ph, u32 ns) {
+    // should_process_event, pod_watcher.py:209
+    if (a.critical_only && ty != kTypeDeleted && ph != kPhNoStatus && ph != kPhFailed && ph != kPhSucceeded) return false;
+    // namespace allow-list, pod_watcher.py:227
+    if (a.ns_filter_on) {
+        const u32 w = ns >> 5;
+        return w < a.ns_words && ((__ldg(a.ns_bitmap + w) >> (ns & 31)) & 1u);
+    }
+    return true;
+}
+
+// Filters + uid interning + record packing.  Thread t of a tile owns events 4t..4t+3 (16-byte vector
+// loads).  The record's position field is always the arrival index of the event.
+// FILTERED == false: no predicate is active, event i becomes record i (two 16-byte streaming stores per thread).
+// FILTERED == true : survivors are compacted in arrival order; tile totals are chained by a decoupled
+//                    look-back, so tiles are handed out by ticket.
+// (Interning in several rounds over L2-sized slices of the dictionary was tried and is slower: the
+//  compaction it needs runs in lock-step generations, and probes that hit L2 only halve the kernel.)
 template <bool FILTERED>
 __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs a) {
     __shared__ u32 s_tot[8];
@@ -129,86 +167,63 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         if (tile >= n_tiles) break;
         const u64 i0 = (u64)tile * kInternTile + (u64)tid * kInternPerThread;
 
-        u64 hi[4], lo[4], rv[4];
-        u32 ns[4], ph[4], ty[4];
+        u64 hi_[4], lo_[4];
+        u32 ph[4], ty[4], ns[4] = {0, 0, 0, 0};
         {
             const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.uid_hi + i0);
             ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
-            hi[0] = x.x; hi[1] = x.y; hi[2] = y.x; hi[3] = y.y;
+            hi_[0] = x.x; hi_[1] = x.y; hi_[2] = y.x; hi_[3] = y.y;
             p = reinterpret_cast<const ulonglong2*>(a.uid_lo + i0);
             x = __ldcs(p); y = __ldcs(p + 1);
-            lo[0] = x.x; lo[1] = x.y; lo[2] = y.x; lo[3] = y.y;
+            lo_[0] = x.x; lo_[1] = x.y; lo_[2] = y.x; lo_[3] = y.y;
         }
         // first probe of all four events in flight before anything else is looked at
         u32 sl[4];
         ulonglong2 pv[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            sl[k] = uid_home_slot(hi[k], lo[k], a.table_mask);
+            sl[k] = uid_home_slot(hi_[k], lo_[k], a.table_mask);
             pv[k] = ld_slot(a.table + sl[k], pol);
         }
         {
-            const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
-            ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
-            rv[0] = x.x; rv[1] = x.y; rv[2] = y.x; rv[3] = y.y;
-            uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.ns + i0));
-            ns[0] = q.x; ns[1] = q.y; ns[2] = q.z; ns[3] = q.w;
-            u32 pw = __ldcs(reinterpret_cast<const u32*>(a.phase + i0));
-            u32 tw = __ldcs(reinterpret_cast<const u32*>(a.type + i0));
+            const u32 pw = __ldcs(reinterpret_cast<const u32*>(a.phase + i0));
+            const u32 tw = __ldcs(reinterpret_cast<const u32*>(a.type + i0));
 #pragma unroll
             for (int k = 0; k < 4; k++) { ph[k] = (pw >> (8 * k)) & 0xFF; ty[k] = (tw >> (8 * k)) & 0xFF; }
-        }
-        // replay order check: rv must not decrease along arrival order
-        {
-            u64 prev = __shfl_up_sync(0xffffffffu, rv[3], 1);
+            if (FILTERED) {
+                const uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.ns + i0));
+                ns[0] = q.x; ns[1] = q.y; ns[2] = q.z; ns[3] = q.w;
+            }
+            // replay order check: rv must not decrease along arrival order
+            const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
+            const ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
+            u64 prev = __shfl_up_sync(0xffffffffu, y.y, 1);
             if (lane == 0) prev = i0 > 0 ? a.rv[i0 - 1] : 0;
-            if (i0 < a.n && rv[0] < prev) flags |= kFlagUnordered;
-#pragma unroll
-            for (int k = 1; k < 4; k++)
-                if (i0 + k < a.n && rv[k] < rv[k - 1]) flags |= kFlagUnordered;
+            if ((i0 < a.n && x.x < prev) || (i0 + 1 < a.n && x.y < x.x) || (i0 + 2 < a.n && y.x < x.y) ||
+                (i0 + 3 < a.n && y.y < y.x))
+                flags |= kFlagUnordered;
         }
         bool keep[4];
         u32 cnt = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             bool ok = i0 + k < a.n;
-            if (ok && (ty[k] > kTypeDeleted || ph[k] > kPhMax || (hi[k] | lo[k]) == 0)) { flags |= kFlagBadEvent; ok = false; }
-            if (FILTERED && ok) {
-                // should_process_event, pod_watcher.py:209
-                if (a.critical_only && ty[k] != kTypeDeleted && ph[k] != kPhNoStatus && ph[k] != kPhFailed &&
-                    ph[k] != kPhSucceeded)
-                    ok = false;
-                // namespace allow-list, pod_watcher.py:227
-                if (ok && a.ns_filter_on) {
-                    u32 w = ns[k] >> 5;
-                    ok = w < a.ns_words && ((__ldg(a.ns_bitmap + w) >> (ns[k] & 31)) & 1u);
-                }
-            }
+            if (ok && (ty[k] > kTypeDeleted || ph[k] > kPhMax || (hi_[k] | lo_[k]) == 0)) { flags |= kFlagBadEvent; ok = false; }
+            if (FILTERED && ok) ok = passes_filters(a, ty[k], ph[k], ns[k]);
             keep[k] = ok;
             cnt += ok;
         }
         u64 dst = i0;
         if (FILTERED) {
+            // stable compaction: this tile's records go behind those of all earlier tiles
             u32 total;
-            u32 local = excl_scan_256(cnt, s_tot, &total);
-            if (tid == 0) {
-                u32 excl = 0;
-                if (tile == 0) {
-                    st_relaxed_u32(a.lookback, kLbInclusive | total);
-                } else {
-                    st_relaxed_u32(a.lookback + tile, kLbPartial | total);
-                    u32 t = tile - 1;
-                    for (;;) {
-                        u32 v = ld_relaxed_u32(a.lookback + t);
-                        if ((v >> 30) == 0) { __nanosleep(20); continue; }
-                        excl += v & kLbValue;
-                        if ((v >> 30) == 2) break;
-                        t--;
-                    }
-                    st_relaxed_u32(a.lookback + tile, kLbInclusive | (excl + total));
+            const u32 local = excl_scan_256(cnt, s_tot, &total);
+            if (tid < 32) {
+                const u32 excl = lookback_scalar_warp(a.lookback, tile, total, lane);
+                if (lane == 0) {
+                    s_tile_excl = excl;
+                    if (tile + 1 == n_tiles) a.ctr->n_survived = (u64)excl + total;   // last tile
                 }
-                s_tile_excl = excl;
-                if (tile + 1 == n_tiles) a.ctr->n_survived = excl + total;   // last tile
             }
             __syncthreads();
             dst = (u64)s_tile_excl + local;
@@ -218,14 +233,13 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         for (int k = 0; k < 4; k++) {
             rec[k] = 0;
             if (keep[k]) {
-                u32 slot = intern_uid(a.table, a.table_mask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
-                const u64 pos = FILTERED ? dst : i0 + k;
-                rec[k] = rec_pack(a.L, slot, pos, ty[k], eff_phase(ph[k]));   // the diff stage compares effective phases
+                const u32 slot = intern_uid(a.table, a.table_mask, hi_[k], lo_[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
+                rec[k] = rec_pack(a.L, slot, i0 + k, ty[k], eff_phase(ph[k]));   // the diff stage compares effective phases
                 del_surv += ty[k] == kTypeDeleted;
 #pragma unroll
                 for (int p = 0; p < 4; p++)
                     if (p < a.key_passes) atomicAdd(&s_hist[p * kRadix + ((slot >> (8 * p)) & 0xFF)], 1u);
-                if (FILTERED) { a.rec_out[dst] = rec[k]; a.origin[dst] = (u32)(i0 + k); dst++; }
+                if (FILTERED) __stcs(a.rec_out + dst++, rec[k]);
             }
         }
         if (!FILTERED) {
@@ -249,6 +263,38 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     }
 }
 
+// R-trace (dedupe off): nothing has to be sorted or interned; the emit bitmap is simply "passes both
+// filters".  One thread per 32 events builds one bitmap word.
+__global__ void __launch_bounds__(256) filter_flag_kernel(InternArgs a, u32* __restrict__ bitmap) {
+    const u32 lane = threadIdx.x & 31;
+    u32 flags = 0;
+    u64 surv = 0, del = 0;
+    const u64 n_words = (a.n + 31) / 32;
+    for (u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (u64)gridDim.x * blockDim.x) {
+        u32 word = 0;
+        u64 prev = w ? a.rv[w * 32 - 1] : 0;
+        for (int b = 0; b < 32; b++) {
+            const u64 i = w * 32 + b;
+            if (i >= a.n) break;
+            const u32 ty = a.type[i], ph = a.phase[i];
+            const u64 rv = a.rv[i];
+            if (rv < prev) flags |= kFlagUnordered;
+            prev = rv;
+            if (ty > kTypeDeleted || ph > kPhMax || (a.uid_hi[i] | a.uid_lo[i]) == 0) { flags |= kFlagBadEvent; continue; }
+            if (passes_filters(a, ty, ph, a.ns[i])) { word |= 1u << b; surv++; del += ty == kTypeDeleted; }
+        }
+        bitmap[w] = word;
+    }
+    surv = __reduce_add_sync(0xffffffffu, (u32)surv);
+    del = __reduce_add_sync(0xffffffffu, (u32)del);
+    flags = __reduce_or_sync(0xffffffffu, flags);
+    if (lane == 0) {
+        if (surv) atomicAdd(&a.ctr->n_survived, surv);
+        if (del) atomicAdd(&a.ctr->n_tombstones, del);
+        if (flags) atomicOr(&a.ctr->flags, flags);
+    }
+}
+
 // ---- segmented adjacent-diff -> emit bitmap ----------------------------------
 // Input: survivors sorted by (key, position).  A record is emitted iff it is a DELETED, opens its
 // key's segment, follows a DELETED of the same key, or carries a different effective phase than
@@ -260,9 +306,9 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
 // that the slice of the bitmap a round touches stays resident in L2 (re-reading the records for
 // every round is cheaper than letting the atomics miss).
 __global__ void __launch_bounds__(256)
-diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout L, Counters* __restrict__ ctr,
-                 u64 pos_lo, u64 pos_hi) {
-    const u64 n = ctr->n_survived;
+diff_flag_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, u32* __restrict__ bitmap, RecLayout L,
+                 Counters* __restrict__ ctr, u64 pos_lo, u64 pos_hi) {
+    const u64 n = *n_ptr;
     const u32 lane = threadIdx.x & 31;
     // records carry the EFFECTIVE phase, and DELETED (type 2) is the only type with bit 7 set, so
     //   emit  <=>  key or phase differs from the predecessor, or either of the two is a DELETED
@@ -297,8 +343,8 @@ diff_flag_kernel(const u64* __restrict__ in, u32* __restrict__ bitmap, RecLayout
 // ---- payload columns --------------------------------------------------------
 // Emitted records -> the columns a sink needs (idx, rv, key, ns_id, phase, type), in replay order.
 struct AssembleArgs {
-    const u32* origin;     // compacted position -> arrival index (NULL: identity)
-    const u32* bitmap;     // emit bit per position (bitmap kernel only)
+    u64 n;                 // positions = events in the log
+    const u32* bitmap;     // emit bit per position
     const u64* rv; const u32* ns; const u8* phase; const u8* type;   // the log
     Counters* ctr;
     u32* lookback;
@@ -306,14 +352,6 @@ struct AssembleArgs {
 };
 
 // The interned key is not written here: few sinks want it, and pte_fetch can look it up on demand.
-__device__ __forceinline__ void assemble_one(const AssembleArgs& a, u64 pos, u64 j) {
-    const u32 idx = a.origin ? a.origin[pos] : (u32)pos;
-    a.out_idx[j] = idx;
-    a.out_rv[j] = __ldcs(a.rv + idx);
-    a.out_ns[j] = __ldcs(a.ns + idx);
-    a.out_phase[j] = __ldcs(a.phase + idx);
-    a.out_type[j] = __ldcs(a.type + idx);
-}
 
 // Interned key of each emitted record, on demand: a read-only walk of the uid dictionary.
 __global__ void __launch_bounds__(256)
@@ -334,23 +372,16 @@ key_lookup_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict_
     }
 }
 
-// R-trace: every survivor is emitted, position == output row.
-__global__ void __launch_bounds__(256) assemble_all_kernel(AssembleArgs a) {
-    const u64 n = a.ctr->n_survived;
-    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
-        assemble_one(a, i, i);
-}
-
-// T-trace: stable compaction of the positions whose emit bit is set.  A tile is 256 bitmap words
+// Stable compaction of the positions whose emit bit is set (T-trace: set by diff_flag_kernel; R-trace: by
+// filter_flag_kernel).  A tile is 256 bitmap words
 // (8192 positions), one word per thread.  The bitmap is small (1 bit per event), so it is read twice:
 // first to count every tile and scan the counts (two tiny kernels), then by the kernel below, whose
 // tiles are independent of each other -- no look-back chain in the kernel that moves the bytes.
 static constexpr int kAsmTile = 256 * 32;
 
 __global__ void __launch_bounds__(256)
-bitmap_count_kernel(const u32* __restrict__ bitmap, const Counters* __restrict__ ctr, u32* __restrict__ tile_count) {
+bitmap_count_kernel(const u32* __restrict__ bitmap, u64 n, u32* __restrict__ tile_count) {
     __shared__ u32 s_w[8];
-    const u64 n = ctr->n_survived;
     const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
     for (u32 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const u64 w = (u64)tile * 256 + threadIdx.x;
@@ -369,9 +400,8 @@ bitmap_count_kernel(const u32* __restrict__ bitmap, const Counters* __restrict__
 }
 
 // exclusive scan of the tile counts, in place, by one block; also the total = n_emitted
-__global__ void __launch_bounds__(1024) tile_scan_kernel(u32* __restrict__ tile_count, Counters* __restrict__ ctr) {
+__global__ void __launch_bounds__(1024) tile_scan_kernel(u32* __restrict__ tile_count, u64 n, Counters* __restrict__ ctr) {
     __shared__ u32 s_part[1024];
-    const u64 n = ctr->n_survived;
     const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
     const u32 per = (n_tiles + 1023) / 1024;
     const u32 lo = min(n_tiles, threadIdx.x * per), hi = min(n_tiles, lo + per);
@@ -393,7 +423,7 @@ __global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a)
     __shared__ unsigned short s_pos[kAsmTile];
     __shared__ u32 s_tot[8];
     const u32 tid = threadIdx.x;
-    const u64 n = a.ctr->n_survived;
+    const u64 n = a.n;
     const u32 n_tiles = (u32)((n + kAsmTile - 1) / kAsmTile);
     for (u32 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const u64 wbase = (u64)tile * 256 + tid;          // bitmap word of this thread
@@ -417,8 +447,7 @@ __global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a)
             for (int k = 0; k < 4; k++) {
                 const u32 j = j0 + k * 256;
                 if (j < cnt) {
-                    const u64 pos = tbase + s_pos[j];
-                    idx[k] = a.origin ? a.origin[pos] : (u32)pos;
+                    idx[k] = (u32)(tbase + s_pos[j]);
                     rv[k] = __ldcs(a.rv + idx[k]);
                     ns[k] = __ldcs(a.ns + idx[k]);
                     ph[k] = __ldcs(a.phase + idx[k]);

@@ -105,8 +105,8 @@ def check_against_oracle(eng, cols, flt, dedupe, pods):
     assert np.array_equal(got.ns_id, cols["ns_id"][i])
     assert np.array_equal(got.phase, cols["phase"][i])
     assert np.array_equal(got.type, cols["type"][i])
-    # the interned key is a bijection of the uid
-    if len(i):
+    # the interned key is a bijection of the uid (keys exist only when the run interned, i.e. dedupe)
+    if len(i) and dedupe:
         uid = cols["uid_hi"][i].astype(object) * (1 << 64) + cols["uid_lo"][i].astype(object)
         pairs = set(zip(uid.tolist(), got.key.tolist()))
         assert len(pairs) == len(set(uid.tolist())) == len(set(got.key.tolist()))
