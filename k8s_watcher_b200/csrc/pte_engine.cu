@@ -86,7 +86,7 @@ struct pte_engine {
     RecLayout L{};
     // sort
     u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // interned records (round-major) + sort ping-pong
-    u32* bitmap = nullptr;                                   // one emit bit per arrival position
+    u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
     int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
@@ -237,7 +237,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv};
     for (void* b : bufs) if (b) cudaFree(b);
@@ -301,7 +301,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
     CKC(dev_alloc(h, &h->table, h->table_cap));
     CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c)); CKC(dev_alloc(h, &h->recC, c));
-    CKC(dev_alloc(h, &h->bitmap, c / 32));
+    CKC(dev_alloc(h, &h->bitmap, c / 32)); CKC(dev_alloc(h, &h->keepmap, c / 32));
     // look-back words: one per (radix tile, digit); also one per intern tile
     u64 min_tile = 2048;
     h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
@@ -466,16 +466,27 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
     a.n = n; a.table = h->table; a.table_mask = (u32)(h->table_cap - 1); a.L = h->L; a.rec_out = h->recA;
     a.ns_bitmap = h->ns_bitmap; a.ns_words = h->ns_words; a.ns_filter_on = h->ns_filter_on;
-    a.critical_only = h->critical_only; a.ctr = h->ctr; a.lookback = h->lookback;
+    a.critical_only = h->critical_only; a.ctr = h->ctr; a.keep = h->keepmap; a.block_off = h->lookback;
     a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
     const u64* n_surv_ptr = &h->ctr->n_survived;
     if (n && dedupe) {
         CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, st));
         const u64 tiles = (n + kInternTile - 1) / kInternTile;
         if (filtered) {
-            CK(h, cudaMemsetAsync(h->lookback, 0, tiles * sizeof(u32), st));
-            int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 4);
+            // predicates -> keep bitmap -> one output offset per 8192-event block -> compacting intern
+            const u64 blocks = (n + kAsmTile - 1) / kAsmTile;
+            int fgrid = (int)std::min<u64>((n / 4 + 255) / 256 + 1, (u64)h->num_sms * 16);
+            filter_flag_kernel<<<fgrid, 256, 0, st>>>(a, h->keepmap);
+            CK(h, cudaGetLastError());
+            bitmap_count_kernel<<<(int)std::min<u64>(blocks, (u64)h->num_sms * 8), 256, 0, st>>>(h->keepmap, n, h->lookback);
+            CK(h, cudaGetLastError());
+            tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, n, h->ctr);
+            CK(h, cudaGetLastError());
+            // filter_flag counted the DELETED survivors as tombstones (right for the R-trace); the diff stage recounts
+            CK(h, cudaMemsetAsync(&h->ctr->n_tombstones, 0, sizeof(u64), st));
+            int grid = (int)std::min<u64>(blocks, (u64)h->num_sms * 8);
             intern_pack_kernel<true><<<grid, kInternThreads, 0, st>>>(a);
+            h->n_launches += 3;
         } else {
             int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
             intern_pack_kernel<false><<<grid, kInternThreads, 0, st>>>(a);
@@ -511,7 +522,7 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         // R-trace: every survivor is emitted; nothing to intern or sort
         CK(h, cudaEventRecord(h->ev[2], st));
         if (n) {
-            int grid = (int)std::min<u64>(((n + 31) / 32 + 255) / 256, (u64)h->num_sms * 16);
+            int grid = (int)std::min<u64>((n / 4 + 255) / 256 + 1, (u64)h->num_sms * 16);
             filter_flag_kernel<<<grid, 256, 0, st>>>(a, h->bitmap);
             CK(h, cudaGetLastError());
             h->n_launches++;

@@ -82,31 +82,6 @@ __device__ __forceinline__ u32 uid_home_slot(u64 hi, u64 lo, u32 mask) {
     return (u32)mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull)) & mask;
 }
 
-// Exclusive prefix of per-tile totals by decoupled look-back, one word per tile, walked by one warp
-// (32 predecessors per step).  Call with all 32 lanes of one warp; every lane gets the result.
-__device__ __forceinline__ u32 lookback_scalar_warp(u32* __restrict__ lb, u32 tile, u32 total, u32 lane) {
-    if (lane == 0) st_relaxed_u32(lb + tile, (tile == 0 ? kLbInclusive : kLbPartial) | total);
-    if (tile == 0) return 0;
-    u32 excl = 0;
-    int t = (int)tile - 1;
-    for (;;) {
-        const int idx = t - (int)lane;
-        const u32 v = idx >= 0 ? ld_relaxed_u32(lb + idx) : kLbInclusive;
-        const u32 not_ready = __ballot_sync(0xffffffffu, (v >> 30) == 0);
-        const u32 inclusive = __ballot_sync(0xffffffffu, (v >> 30) == 2);
-        const int first_nr = not_ready ? __ffs(not_ready) - 1 : 32;
-        const int first_in = inclusive ? __ffs(inclusive) - 1 : 32;
-        const bool done = first_in < first_nr;
-        const int last = done ? first_in : first_nr - 1;            // lanes 0..last are summed
-        excl += __reduce_add_sync(0xffffffffu, (int)lane <= last ? (v & kLbValue) : 0u);
-        if (done) break;
-        t -= first_nr;
-        if (first_nr == 0) __nanosleep(40);
-    }
-    if (lane == 0) st_relaxed_u32(lb + tile, kLbInclusive | (excl + total));
-    return excl;
-}
-
 struct InternArgs {
     const u64* uid_hi; const u64* uid_lo; const u64* rv;
     const u32* ns; const u8* phase; const u8* type;
@@ -116,11 +91,13 @@ struct InternArgs {
     u64* rec_out;
     const u32* ns_bitmap; u32 ns_words; int ns_filter_on; int critical_only;
     Counters* ctr;
-    u32* lookback;     // one word per tile, zeroed (FILTERED only)
+    const u32* keep;       // FILTERED: keep bitmap written by filter_flag_kernel
+    const u32* block_off;  // FILTERED: records before each 8192-event block (tile_scan_kernel)
     u32* hist;         // digit counts of the key field for the radix passes that follow
     int key_passes;    // number of 8-bit digits in the key field (<= 4)
 };
 
+static constexpr int kAsmTile = 256 * 32;       // positions per bitmap tile (256 words)
 static constexpr int kInternThreads = 256;
 static constexpr int kInternPerThread = 4;
 static constexpr int kInternTile = kInternThreads * kInternPerThread;
@@ -137,17 +114,18 @@ __device__ __forceinline__ bool passes_filters(const InternArgs& a, u32 ty, u32 
     return true;
 }
 
-// Filters + uid interning + record packing.  Thread t of a tile owns events 4t..4t+3 (16-byte vector
+// uid interning + record packing.  Thread t of a 1024-event tile owns events 4t..4t+3 (16-byte vector
 // loads).  The record's position field is always the arrival index of the event.
 // FILTERED == false: no predicate is active, event i becomes record i (two 16-byte streaming stores per thread).
-// FILTERED == true : survivors are compacted in arrival order; tile totals are chained by a decoupled
-//                    look-back, so tiles are handed out by ticket.
-// (Interning in several rounds over L2-sized slices of the dictionary was tried and is slower: the
-//  compaction it needs runs in lock-step generations, and probes that hit L2 only halve the kernel.)
+// FILTERED == true : filter_flag_kernel has already evaluated the reference's predicates into a keep
+//                    bitmap, and bitmap_count/tile_scan have turned it into one output offset per
+//                    8192-event block; survivors are compacted in arrival order behind that offset.  No
+//                    ticket and no look-back: the blocks are independent.
+// (Interning in several rounds over L2-sized slices of the dictionary was tried and is slower: probes
+//  that hit L2 only halve the kernel, and every round has to re-read the uid columns.)
 template <bool FILTERED>
 __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs a) {
     __shared__ u32 s_tot[8];
-    __shared__ u32 s_tile, s_tile_excl;
     __shared__ u32 s_hist[4 * kRadix];     // the sort's digit counts are taken here: no extra read of the records
     const u32 tid = threadIdx.x, lane = tid & 31;
     u32 inserted = 0, del_surv = 0, flags = 0;
@@ -156,19 +134,19 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     __syncthreads();
     const u32 n_tiles = (u32)((a.n + kInternTile - 1) / kInternTile);
     const u64 pol = l2_policy_evict_last();
+    constexpr u32 kSub = kAsmTile / kInternTile;          // 1024-event tiles per 8192-event block
+    u32 run = 0, cur_block = ~0u;                         // FILTERED: records written so far in the current block
 
-    for (u32 tile = blockIdx.x;; tile += gridDim.x) {
-        if (FILTERED) {            // look-back needs tiles handed out in order
-            __syncthreads();
-            if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket[0], 1u);
-            __syncthreads();
-            tile = s_tile;
-        }
+    // FILTERED walks whole 8192-event blocks (its tiles must come in order inside a block)
+    const u32 step = FILTERED ? gridDim.x * kSub : gridDim.x;
+    for (u32 tile0 = FILTERED ? blockIdx.x * kSub : blockIdx.x; tile0 < n_tiles; tile0 += step)
+    for (u32 sub = 0; sub < (FILTERED ? kSub : 1u); sub++) {
+        const u32 tile = tile0 + sub;
         if (tile >= n_tiles) break;
         const u64 i0 = (u64)tile * kInternTile + (u64)tid * kInternPerThread;
 
         u64 hi_[4], lo_[4];
-        u32 ph[4], ty[4], ns[4] = {0, 0, 0, 0};
+        u32 ph[4], ty[4];
         {
             const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.uid_hi + i0);
             ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
@@ -177,24 +155,26 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
             x = __ldcs(p); y = __ldcs(p + 1);
             lo_[0] = x.x; lo_[1] = x.y; lo_[2] = y.x; lo_[3] = y.y;
         }
-        // first probe of all four events in flight before anything else is looked at
+        // keep bits of this thread's four events (bit k = event i0+k)
+        u32 keep_bits = 0xFu;
+        if (FILTERED) keep_bits = (a.keep[i0 >> 5] >> (i0 & 31)) & 0xFu;
+        // first probe of all kept events in flight before anything else is looked at
         u32 sl[4];
         ulonglong2 pv[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             sl[k] = uid_home_slot(hi_[k], lo_[k], a.table_mask);
-            pv[k] = ld_slot(a.table + sl[k], pol);
+            pv[k] = make_ulonglong2(0, 0);
+            if (!FILTERED || ((keep_bits >> k) & 1u)) pv[k] = ld_slot(a.table + sl[k], pol);
         }
         {
             const u32 pw = __ldcs(reinterpret_cast<const u32*>(a.phase + i0));
             const u32 tw = __ldcs(reinterpret_cast<const u32*>(a.type + i0));
 #pragma unroll
             for (int k = 0; k < 4; k++) { ph[k] = (pw >> (8 * k)) & 0xFF; ty[k] = (tw >> (8 * k)) & 0xFF; }
-            if (FILTERED) {
-                const uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.ns + i0));
-                ns[0] = q.x; ns[1] = q.y; ns[2] = q.z; ns[3] = q.w;
-            }
-            // replay order check: rv must not decrease along arrival order
+        }
+        if (!FILTERED) {
+            // replay order check: rv must not decrease along arrival order (filter_flag_kernel does it for FILTERED)
             const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);
             const ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
             u64 prev = __shfl_up_sync(0xffffffffu, y.y, 1);
@@ -207,26 +187,21 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
         u32 cnt = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            bool ok = i0 + k < a.n;
-            if (ok && (ty[k] > kTypeDeleted || ph[k] > kPhMax || (hi_[k] | lo_[k]) == 0)) { flags |= kFlagBadEvent; ok = false; }
-            if (FILTERED && ok) ok = passes_filters(a, ty[k], ph[k], ns[k]);
+            bool ok = i0 + k < a.n && ((keep_bits >> k) & 1u);
+            if (ok && (ty[k] > kTypeDeleted || ph[k] > kPhMax)) { flags |= kFlagBadEvent; ok = FILTERED; }   // the run fails anyway
+            if (ok && (hi_[k] | lo_[k]) == 0) { flags |= kFlagBadEvent; ok = FILTERED; }
             keep[k] = ok;
             cnt += ok;
         }
         u64 dst = i0;
         if (FILTERED) {
-            // stable compaction: this tile's records go behind those of all earlier tiles
+            // stable compaction behind the block's scanned offset
+            const u32 block = tile / kSub;
+            if (block != cur_block) { cur_block = block; run = a.block_off[block]; }
             u32 total;
             const u32 local = excl_scan_256(cnt, s_tot, &total);
-            if (tid < 32) {
-                const u32 excl = lookback_scalar_warp(a.lookback, tile, total, lane);
-                if (lane == 0) {
-                    s_tile_excl = excl;
-                    if (tile + 1 == n_tiles) a.ctr->n_survived = (u64)excl + total;   // last tile
-                }
-            }
-            __syncthreads();
-            dst = (u64)s_tile_excl + local;
+            dst = (u64)run + local;
+            run += total;
         }
         u64 rec[4];
 #pragma unroll
@@ -234,7 +209,7 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
             rec[k] = 0;
             if (keep[k]) {
                 const u32 slot = intern_uid(a.table, a.table_mask, hi_[k], lo_[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
-                rec[k] = rec_pack(a.L, slot, i0 + k, ty[k], eff_phase(ph[k]));   // the diff stage compares effective phases
+                rec[k] = rec_pack(a.L, slot, i0 + k, ty[k] & 3u, eff_phase(ph[k]) & 63u);   // the diff stage compares effective phases
                 del_surv += ty[k] == kTypeDeleted;
 #pragma unroll
                 for (int p = 0; p < 4; p++)
@@ -263,34 +238,49 @@ __global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs 
     }
 }
 
-// R-trace (dedupe off): nothing has to be sorted or interned; the emit bitmap is simply "passes both
-// filters".  One thread per 32 events builds one bitmap word.
+// The reference's two predicates for every event -> keep bitmap (one bit per arrival position), plus the
+// replay-order check.  For the R-trace (dedupe off) this bitmap already is the emit bitmap: nothing has to
+// be interned or sorted.  For filtered T-trace runs it drives the compaction in intern_pack_kernel.
+// Four events per thread (16-byte loads); eight threads' nibbles make one bitmap word.
 __global__ void __launch_bounds__(256) filter_flag_kernel(InternArgs a, u32* __restrict__ bitmap) {
     const u32 lane = threadIdx.x & 31;
-    u32 flags = 0;
-    u64 surv = 0, del = 0;
-    const u64 n_words = (a.n + 31) / 32;
-    for (u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (u64)gridDim.x * blockDim.x) {
-        u32 word = 0;
-        u64 prev = w ? a.rv[w * 32 - 1] : 0;
-        for (int b = 0; b < 32; b++) {
-            const u64 i = w * 32 + b;
-            if (i >= a.n) break;
-            const u32 ty = a.type[i], ph = a.phase[i];
-            const u64 rv = a.rv[i];
-            if (rv < prev) flags |= kFlagUnordered;
-            prev = rv;
-            if (ty > kTypeDeleted || ph > kPhMax || (a.uid_hi[i] | a.uid_lo[i]) == 0) { flags |= kFlagBadEvent; continue; }
-            if (passes_filters(a, ty, ph, a.ns[i])) { word |= 1u << b; surv++; del += ty == kTypeDeleted; }
+    u32 flags = 0, surv = 0, del = 0;
+    const u64 n4 = (a.n + 3) / 4;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    // warp-uniform loop bound: every lane takes part in the shuffles
+    for (u64 wb = (u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); wb < n4; wb += stride) {
+        const u64 i0 = (wb + lane) * 4;
+        const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.rv + i0);       // padded: readable past n
+        const ulonglong2 x = __ldcs(p), y = __ldcs(p + 1);
+        const uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.ns + i0));
+        const u32 pw = __ldcs(reinterpret_cast<const u32*>(a.phase + i0));
+        const u32 tw = __ldcs(reinterpret_cast<const u32*>(a.type + i0));
+        u64 prev = __shfl_up_sync(0xffffffffu, y.y, 1);
+        if (lane == 0) prev = i0 > 0 ? a.rv[i0 - 1] : 0;
+        if ((i0 < a.n && x.x < prev) || (i0 + 1 < a.n && x.y < x.x) || (i0 + 2 < a.n && y.x < x.y) ||
+            (i0 + 3 < a.n && y.y < y.x))
+            flags |= kFlagUnordered;
+        const u32 ns[4] = {q.x, q.y, q.z, q.w};
+        u32 nib = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const u32 ty = (tw >> (8 * k)) & 0xFF, ph = (pw >> (8 * k)) & 0xFF;
+            if (i0 + k >= a.n) continue;
+            if (ty > kTypeDeleted || ph > kPhMax) { flags |= kFlagBadEvent; continue; }
+            if (passes_filters(a, ty, ph, ns[k])) { nib |= 1u << k; surv++; del += ty == kTypeDeleted; }
         }
-        bitmap[w] = word;
+        u32 w = nib << (4 * (lane & 7));
+        w |= __shfl_xor_sync(0xffffffffu, w, 1);
+        w |= __shfl_xor_sync(0xffffffffu, w, 2);
+        w |= __shfl_xor_sync(0xffffffffu, w, 4);
+        if ((lane & 7) == 0 && i0 < a.n) bitmap[i0 >> 5] = w;
     }
-    surv = __reduce_add_sync(0xffffffffu, (u32)surv);
-    del = __reduce_add_sync(0xffffffffu, (u32)del);
+    surv = __reduce_add_sync(0xffffffffu, surv);
+    del = __reduce_add_sync(0xffffffffu, del);
     flags = __reduce_or_sync(0xffffffffu, flags);
     if (lane == 0) {
-        if (surv) atomicAdd(&a.ctr->n_survived, surv);
-        if (del) atomicAdd(&a.ctr->n_tombstones, del);
+        if (surv) atomicAdd(&a.ctr->n_survived, (u64)surv);
+        if (del) atomicAdd(&a.ctr->n_tombstones, (u64)del);
         if (flags) atomicOr(&a.ctr->flags, flags);
     }
 }
@@ -377,7 +367,6 @@ key_lookup_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict_
 // (8192 positions), one word per thread.  The bitmap is small (1 bit per event), so it is read twice:
 // first to count every tile and scan the counts (two tiny kernels), then by the kernel below, whose
 // tiles are independent of each other -- no look-back chain in the kernel that moves the bytes.
-static constexpr int kAsmTile = 256 * 32;
 
 __global__ void __launch_bounds__(256)
 bitmap_count_kernel(const u32* __restrict__ bitmap, u64 n, u32* __restrict__ tile_count) {
