@@ -68,7 +68,7 @@ typedef struct pte_stats {
     float ms_total;         /* device time of this pte_run, CUDA events on the engine stream */
     float ms_intern;        /* filter + uid interning + record packing */
     float ms_sort_key;      /* LSD radix passes on the interned key */
-    float ms_diff;          /* segmented adjacent-diff -> emit bitmap */
+    float ms_diff;          /* segmented adjacent-diff -> emit bitmap (dedupe == 0: the predicate bitmap kernel) */
     float ms_sort_order;    /* always 0 since replay order is restored by the bitmap scan in ms_assemble */
     float ms_assemble;      /* bitmap scan + compaction in replay order + payload columns */
     float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
