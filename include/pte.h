@@ -62,7 +62,7 @@ typedef struct pte_stats {
     uint64_t n_survived;    /* passed should_process_event (:204-212) and the namespace list (:226-229) */
     uint64_t n_emitted;     /* notifications (R-trace if dedupe == 0, T-trace otherwise) */
     uint64_t n_tombstones;  /* emitted DELETED events */
-    uint64_t n_pods;        /* distinct uids interned so far on this handle */
+    uint64_t n_pods;        /* distinct uids in the dictionary (cumulative over a PTE_RUN_CARRY stream) */
     uint32_t ordered;       /* 1: rv was non-decreasing in arrival order */
     uint32_t n_launches;    /* kernels launched by this pte_run */
     float ms_total;         /* device time of this pte_run, CUDA events on the engine stream */
@@ -134,11 +134,17 @@ int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv,
 
 /* Replay the device-resident log: filters -> uid interning -> LSD radix sort on (key, rv) ->
  * segmented adjacent-diff -> emit bitmap -> scan of the bitmap in replay order -> payload columns.
- * dedupe == 0: every event that would reach the POST site (pod_watcher.py:232-236), the R-trace.
- * dedupe != 0: only phase transitions and DELETED tombstones (the last-known-phase layer the
- *              reference's README describes but pod_watcher.py does not implement), the T-trace.
- * The interning dictionary is cleared at the start of every call. */
-int pte_run(pte_handle h, int dedupe, pte_stats* out);
+ * flags = 0               : every event that would reach the POST site (pod_watcher.py:232-236), the R-trace.
+ * flags & PTE_RUN_DEDUPE  : only phase transitions and DELETED tombstones (the last-known-phase layer the
+ *                           reference's README describes but pod_watcher.py does not implement), the T-trace.
+ * flags & PTE_RUN_CARRY   : (with DEDUPE) the log is the next batch of a stream: the uid dictionary and the
+ *                           last known phase of every pod are kept from the previous PTE_RUN_CARRY call on
+ *                           this handle, so that micro-batches of the live loop (pod_watcher.py:264-269) give
+ *                           exactly the notifications one replay of the whole stream would.  A call without
+ *                           the flag, or a failed call, ends the stream; the next CARRY call starts a new one.
+ * Without PTE_RUN_CARRY the dictionary is cleared at the start of the call. */
+enum { PTE_RUN_DEDUPE = 1, PTE_RUN_CARRY = 2 };
+int pte_run(pte_handle h, int flags, pte_stats* out);
 
 /* Emitted records of the last pte_run, in replay order, into caller columns (any may be NULL):
  * idx = arrival index in the ingested log, key = interned 64-bit uid key (dedupe runs only; ~0 otherwise).

@@ -87,6 +87,9 @@ struct pte_engine {
     // sort
     u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // interned records (round-major) + sort ping-pong
     u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
+    u8 *state_old = nullptr, *state_new = nullptr;           // per dictionary slot: last known phase of the stream
+    bool carry_valid = false;                                // dictionary + state hold a stream that can be continued
+    u64 pods_total = 0, stream_last_rv = 0, batch_first_rv = 0, batch_last_rv = 0;
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
     int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
@@ -237,7 +240,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv};
     for (void* b : bufs) if (b) cudaFree(b);
@@ -300,6 +303,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKC(dev_alloc(h, &h->uid_hi, c)); CKC(dev_alloc(h, &h->uid_lo, c)); CKC(dev_alloc(h, &h->rv, c));
     CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
     CKC(dev_alloc(h, &h->table, h->table_cap));
+    CKC(dev_alloc(h, &h->state_old, h->table_cap)); CKC(dev_alloc(h, &h->state_new, h->table_cap));
     CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c)); CKC(dev_alloc(h, &h->recC, c));
     CKC(dev_alloc(h, &h->bitmap, c / 32)); CKC(dev_alloc(h, &h->keepmap, c / 32));
     // look-back words: one per (radix tile, digit); also one per intern tile
@@ -358,6 +362,8 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
     }
     h->n_events = n;
     h->has_run = false;
+    h->batch_first_rv = n ? rv[0] : 0;
+    h->batch_last_rv = n ? rv[n - 1] : 0;
     return PTE_OK;
 }
 
@@ -450,16 +456,26 @@ int pte_generate(pte_handle h, const pte_gen_params* p) {
     return PTE_OK;
 }
 
-int pte_run(pte_handle h, int dedupe, pte_stats* out) {
+int pte_run(pte_handle h, int flags, pte_stats* out) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     CK(h, cudaSetDevice(h->device));
+    const int dedupe = flags & PTE_RUN_DEDUPE;
+    const bool carry = dedupe && (flags & PTE_RUN_CARRY);
     const u64 n = h->n_events;
+    if (carry && h->carry_valid && n && h->batch_first_rv < h->stream_last_rv)
+        FAIL(h, PTE_ERR_UNORDERED, "this batch starts at a resourceVersion below the end of the previous batch of the stream");
     h->n_launches = 0;
     h->pass_ev_used = 0;
     h->has_run = false;
     cudaStream_t st = h->stream;
     CK(h, cudaEventRecord(h->ev[0], st));
-    CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
+    const bool fresh = !(carry && h->carry_valid);       // start from an empty dictionary
+    if (fresh) {
+        CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
+        if (carry) CK(h, cudaMemsetAsync(h->state_old, 0, h->table_cap, st));
+        h->pods_total = 0;
+    }
+    if (carry) CK(h, cudaMemcpyAsync(h->state_new, h->state_old, h->table_cap, cudaMemcpyDeviceToDevice, st));
     CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
     const bool filtered = h->critical_only || h->ns_filter_on;
     InternArgs a;
@@ -514,7 +530,9 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
         const u64 drounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
         const u64 span = round_up((n + drounds - 1) / drounds, 32);
         for (u64 r = 0; r < drounds; r++) {
-            diff_flag_kernel<<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, r * span, std::min(n, (r + 1) * span));
+            const u64 plo = r * span, phi = std::min(n, (r + 1) * span);
+            if (carry) diff_flag_kernel<true><<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, plo, phi, h->state_old, h->state_new);
+            else diff_flag_kernel<false><<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, plo, phi, nullptr, nullptr);
             CK(h, cudaGetLastError());
             h->n_launches++;
         }
@@ -546,13 +564,16 @@ int pte_run(pte_handle h, int dedupe, pte_stats* out) {
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
     int rc = check_flags(h, h->last.flags);
-    if (rc) return rc;
+    if (rc) { h->carry_valid = false; return rc; }
+    h->pods_total += h->last.n_pods;
+    if (carry) { std::swap(h->state_old, h->state_new); h->stream_last_rv = n ? h->batch_last_rv : h->stream_last_rv; }
+    h->carry_valid = carry;
     h->has_run = true;
     h->key_valid = false;
     if (out) {
         memset(out, 0, sizeof(*out));
         out->n_in = n; out->n_survived = h->last.n_survived; out->n_emitted = h->last.n_emitted;
-        out->n_tombstones = h->last.n_tombstones; out->n_pods = h->last.n_pods;
+        out->n_tombstones = h->last.n_tombstones; out->n_pods = h->pods_total;
         out->ordered = 1; out->n_launches = h->n_launches;
         cudaEventElapsedTime(&out->ms_total, h->ev[0], h->ev[5]);
         cudaEventElapsedTime(&out->ms_intern, h->ev[0], h->ev[1]);

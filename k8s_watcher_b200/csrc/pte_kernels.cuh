@@ -295,30 +295,55 @@ __global__ void __launch_bounds__(256) filter_flag_kernel(InternArgs a, u32* __r
 // One launch covers the positions [pos_lo, pos_hi): the host splits the position space into rounds so
 // that the slice of the bitmap a round touches stays resident in L2 (re-reading the records for
 // every round is cheaper than letting the atomics miss).
+// CARRY: the dictionary and one state byte per slot (0 = no live phase known, else 1 + effective phase)
+// survive from the previous batches of a stream.  The first record of a key then compares against that
+// state instead of being emitted unconditionally, and the last record of a key leaves the new state.
+// Heads read state_old, tails write state_new (a copy of state_old made before the launch), so the
+// rounds and the threads of one round cannot see each other's updates.
+template <bool CARRY>
 __global__ void __launch_bounds__(256)
 diff_flag_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, u32* __restrict__ bitmap, RecLayout L,
-                 Counters* __restrict__ ctr, u64 pos_lo, u64 pos_hi) {
+                 Counters* __restrict__ ctr, u64 pos_lo, u64 pos_hi, const u8* __restrict__ state_old,
+                 u8* __restrict__ state_new) {
     const u64 n = *n_ptr;
     const u32 lane = threadIdx.x & 31;
     // records carry the EFFECTIVE phase, and DELETED (type 2) is the only type with bit 7 set, so
     //   emit  <=>  key or phase differs from the predecessor, or either of the two is a DELETED
-    const u64 diff_mask = (~0ull << L.key_shift()) | 0x3Full;
+    const u32 ks = L.key_shift();
+    const u64 diff_mask = (~0ull << ks) | 0x3Full;
     const u64 pos_mask = L.idx_mask() << 8, lo8 = pos_lo << 8, hi8 = pos_hi << 8;
     u32 tomb = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x * 2;
-    // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffle
+    // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffles
     for (u64 wb = ((u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) * 2; wb < n; wb += stride) {
         const u64 i = wb + lane * 2;
         const ulonglong2 c = __ldcs(reinterpret_cast<const ulonglong2*>(in + i));   // padded: readable past n
         u64 p = __shfl_up_sync(0xffffffffu, c.y, 1);
         if (lane == 0) p = i > 0 ? in[i - 1] : ~c.x;                                  // ~c.x: a different key
+        u64 nxt = 0;
+        if (CARRY) {
+            nxt = __shfl_down_sync(0xffffffffu, c.x, 1);
+            if (lane == 31) nxt = in[i + 2];
+        }
         const u64 r[2] = {c.x, c.y};
 #pragma unroll
         for (int k = 0; k < 2; k++) {
             const u64 cur = r[k];
-            const bool emit = ((((p ^ cur) & diff_mask) | ((p | cur) & 0x80ull)) != 0) && i + k < n;
+            const bool valid = i + k < n;
+            bool emit = (((p ^ cur) & diff_mask) | ((p | cur) & 0x80ull)) != 0;
             const u64 pos8 = cur & pos_mask;
-            if (emit && pos8 >= lo8 && pos8 < hi8) {
+            const bool mine = valid && pos8 >= lo8 && pos8 < hi8;
+            if (CARRY && mine) {
+                const u32 slot = (u32)(cur >> ks);
+                if ((p >> ks) != (cur >> ks)) {                       // first record of this key in the batch
+                    const u32 st = state_old[slot];
+                    emit = (cur & 0x80ull) || st == 0 || st - 1 != (u32)(cur & 0x3F);
+                }
+                const u64 nx = k == 0 ? r[1] : nxt;
+                if (i + k + 1 >= n || (nx >> ks) != (cur >> ks))      // last record of this key in the batch
+                    state_new[slot] = (cur & 0x80ull) ? (u8)0 : (u8)(1 + (cur & 0x3F));
+            }
+            if (emit && mine) {
                 const u64 pos = pos8 >> 8;
                 atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
                 tomb += (u32)(cur >> 7) & 1u;

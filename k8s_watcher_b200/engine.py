@@ -173,9 +173,12 @@ class PhaseTransitionEngine:
         return cols
 
     # -- the hot path
-    def run(self, dedupe: bool = True) -> Dict[str, float]:
+    def run(self, dedupe: bool = True, carry: bool = False) -> Dict[str, float]:
+        """Replay the resident log.  ``carry`` continues a stream: dictionary and per-pod last phase are kept
+        from the previous ``carry`` run, so consecutive batches add up to one replay of the whole stream."""
         st = PteStats()
-        self._ck(self._L.pte_run(self._h, int(bool(dedupe)), C.byref(st)))
+        flags = (1 if dedupe else 0) | (2 if carry and dedupe else 0)
+        self._ck(self._L.pte_run(self._h, flags, C.byref(st)))
         self.last_stats = st.as_dict()
         return self.last_stats
 

@@ -64,7 +64,8 @@ class Batch:
 class PodWatcher:
     def __init__(self, environment: str = "development", *, dedupe: bool = True,
                  sink: Optional[ClusterApiClient] = None, engine: Optional[PhaseTransitionEngine] = None,
-                 device: int = 0, config_dir: str = "config"):
+                 device: int = 0, config_dir: str = "config", flush_every: Optional[int] = None,
+                 max_pods: int = 1 << 20):
         self.environment = environment
         self.config_dir = config_dir           # CWD-relative by default, like upstream (:22,:25)
         self.config = self._load_environment_config()
@@ -77,6 +78,11 @@ class PodWatcher:
         self._device = device
         self._pending: List[Dict[str, Any]] = []
         self.batches: List[Batch] = []
+        # live loop: replay every `flush_every` queued events as one batch of a stream; the engine carries the
+        # uid dictionary and each pod's last known phase from batch to batch (None: one replay at stream end)
+        self.flush_every = flush_every
+        self.max_pods = max_pods
+        self._stream_namespaces: List[str] = []      # namespace dictionary shared by all batches of a stream
 
     # ---- configuration (pod_watcher.py:19-75) ---------------------------------
     def _load_environment_config(self) -> Dict[str, Any]:
@@ -206,6 +212,8 @@ class PodWatcher:
     def handle_pod_event(self, event_type: str, pod) -> None:
         """Queue one event for the next bulk replay (the reference decides per event, :214-241)."""
         self._pending.append({"type": event_type, "object": pod})
+        if self.flush_every and len(self._pending) >= self.flush_every:
+            self.flush()
 
     # ---- bulk path -----------------------------------------------------------------
     def _engine_for(self, n_events: int, n_pods_hint: int) -> PhaseTransitionEngine:
@@ -216,14 +224,20 @@ class PodWatcher:
             eng = self._engine = PhaseTransitionEngine(max(n_events, 1024), max(n_pods_hint, 0), device=self._device)
         return eng
 
-    def replay(self, log: ReplayLog, *, dedupe: Optional[bool] = None, max_pods: int = 0) -> Batch:
-        """Run a whole log through the engine and return what a watcher would have notified."""
+    def replay(self, log: ReplayLog, *, dedupe: Optional[bool] = None, max_pods: int = 0, carry: bool = False) -> Batch:
+        """Run a whole log through the engine and return what a watcher would have notified.
+        ``carry=True`` treats the log as the next batch of a stream (state kept on the device)."""
         dedupe = self.dedupe if dedupe is None else dedupe
-        eng = self._engine_for(len(log), max_pods)
+        if carry and self._engine is None:
+            self._engine = PhaseTransitionEngine(max(self.flush_every or len(log), len(log), 1024), self.max_pods,
+                                                 device=self._device)
+        if carry and self._engine.max_events < len(log):
+            raise ValueError("a stream batch of %d events exceeds the engine's %d" % (len(log), self._engine.max_events))
+        eng = self._engine if carry else self._engine_for(len(log), max_pods)
         names = self.config.get("watcher", {}).get("namespaces", []) or []
         eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
         eng.ingest(log.columns)
-        stats = eng.run(dedupe=dedupe)
+        stats = eng.run(dedupe=dedupe, carry=carry)
         # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
         self.batches.append(batch)
@@ -233,9 +247,9 @@ class PodWatcher:
         """Replay everything queued by handle_pod_event; hand the result to the sink if there is one."""
         if not self._pending:
             return None
-        log = ReplayLog.from_events(self._pending)
+        log = ReplayLog.from_events(self._pending, namespaces=self._stream_namespaces)
         self._pending = []
-        batch = self.replay(log)
+        batch = self.replay(log, carry=bool(self.flush_every))
         if self.clusterapi_client is not None:
             sent = self.clusterapi_client.update_pod_status_batch(batch)
             if sent != len(batch):

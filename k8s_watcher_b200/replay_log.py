@@ -33,12 +33,14 @@ class ReplayLog:
 
     # ---- construction -------------------------------------------------------
     @classmethod
-    def from_events(cls, events: Iterable[Dict[str, Any]]) -> "ReplayLog":
-        """Intern a stream of ``{'type': str, 'object': V1Pod}`` dicts (pod_watcher.py:267-268)."""
+    def from_events(cls, events: Iterable[Dict[str, Any]], namespaces: Optional[List[str]] = None) -> "ReplayLog":
+        """Intern a stream of ``{'type': str, 'object': V1Pod}`` dicts (pod_watcher.py:267-268).
+        ``namespaces`` is an optional, growing id -> name list shared between the batches of one stream."""
         events = list(events)
         n = len(events)
         cols = {name: np.zeros(n, dt) for name, dt in COLUMNS}
-        ns_ids: Dict[str, int] = {}
+        shared = namespaces if namespaces is not None else []
+        ns_ids: Dict[str, int] = {name: i for i, name in enumerate(shared)}
         phase_ids: Dict[Any, int] = {p: i for i, p in enumerate(codes.PHASE_NAMES)}
         phases: List[Any] = list(codes.PHASE_NAMES) + [None, None]
         pods = []
@@ -72,6 +74,7 @@ class ReplayLog:
         names = [None] * len(ns_ids)
         for k, v in ns_ids.items():
             names[v] = k
+        shared[:] = names
         return cls(cols, names, phases, pods)
 
     @classmethod

@@ -315,3 +315,67 @@ def test_live_loop_surface_with_mock_sink(monkeypatch):
         want = dict(fx["payloads"][k])
         b.pop("event_timestamp"), want.pop("event_timestamp")       # wall clock, pod_watcher.py:199
         assert b == want
+
+
+# ---- streams: state carried on the device from batch to batch ---------------------
+@pytest.mark.parametrize("env", list(FILTERS))
+@pytest.mark.parametrize("cuts", [(0.5,), (0.1, 0.11, 0.6), (0.0, 0.3, 0.3, 1.0)])
+def test_carried_batches_equal_one_replay(env, cuts):
+    n, pods = 120_000, 900
+    cols = c_oracle.generate(SEED + 5, n, pods, dist=1, p_del=0.08, p_nostatus=0.03, p_null=0.03)
+    flt = FILTERS[env]
+    want, ost, _ = c_oracle.replay(cols, critical_only=flt["critical_only"], ns_allow=flt["ns_allow"], pods_hint=pods)
+    edges = [0] + [int(c * n) for c in cuts] + [n]
+    got, tomb = [], 0
+    with PhaseTransitionEngine(n, pods) as e:
+        e.set_filters(flt["ns_allow"], critical_only=flt["critical_only"])
+        for lo, hi in zip(edges[:-1], edges[1:]):
+            e.ingest({k: v[lo:hi] for k, v in cols.items()})
+            st = e.run(dedupe=True, carry=True)
+            got.append(e.fetch(columns=("idx",)).idx.astype(np.int64) + lo)
+            tomb += st["n_tombstones"]
+        assert np.array_equal(np.concatenate(got), want.astype(np.int64))
+        assert tomb == ost["n_tombstones"] and st["n_pods"] <= pods
+        # a run without the flag ends the stream: the same last batch replayed alone starts from scratch
+        alone, _, _ = c_oracle.replay({k: v[lo:hi] for k, v in cols.items()}, critical_only=flt["critical_only"],
+                                      ns_allow=flt["ns_allow"])
+        e.run(dedupe=True)
+        assert np.array_equal(e.fetch(columns=("idx",)).idx.astype(np.uint64), alone)
+        # ... and the next carry run opens a NEW stream (no leftovers from the old one)
+        e.run(dedupe=True, carry=True)
+        assert np.array_equal(e.fetch(columns=("idx",)).idx.astype(np.uint64), alone)
+
+
+def test_stream_batches_must_not_go_back_in_time():
+    cols = c_oracle.generate(3, 2000, 50)
+    with PhaseTransitionEngine(2000, 50) as e:
+        e.ingest({k: v[1000:] for k, v in cols.items()})
+        e.run(carry=True)
+        e.ingest({k: v[:1000] for k, v in cols.items()})
+        with pytest.raises(PteError) as ei:
+            e.run(carry=True)
+        assert ei.value.code == -7
+
+
+def test_live_loop_micro_batches_match_one_replay(monkeypatch):
+    """start_watching() with flush_every: the sink sees exactly the transitions of the whole stream."""
+    from k8s_watcher_b200 import ClusterApiClient, _k8s_stub
+    fx = _load([p for p in GOLDEN if "edge_development" in p][0])
+    monkeypatch.chdir(ROOT)
+    events = fk.events_from_columns(fx["cols"])
+    _k8s_stub.queue_events(events)
+    fk.set_stream(events)
+    sink = ClusterApiClient("http://clusterapi.invalid")
+    w = PodWatcher("staging", sink=sink, flush_every=64, max_pods=64)
+    cfg = dict(fx["config"])
+    cfg.pop("kubernetes", None)                                    # no kubeconfig file here: default set-up path
+    w.environment, w.config = "development", cfg                   # development's namespace filter
+    w.start_watching()
+    assert len(w.batches) == -(-len(events) // 64)
+    keep = po.transition_filter(fx["payloads"])
+    bodies = [json.loads(b) for b in sink.transport.bodies()]
+    assert [b["uid"] for b in bodies] == [fx["payloads"][k]["uid"] for k in keep]
+    for b, k in zip(bodies, keep):
+        want = dict(fx["payloads"][k])
+        b.pop("event_timestamp"), want.pop("event_timestamp")
+        assert b == want
