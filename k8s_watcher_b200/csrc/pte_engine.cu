@@ -95,6 +95,7 @@ struct pte_engine {
     int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
     u64 diff_round_bytes = 64ull << 20;      // bitmap bytes one diff round may touch
     bool key_valid = false;                  // out_key holds the keys of the last run
+    bool no_invert = false;                  // PTE_NO_INVERT=1: always set emitted bits (tuning / tests)
     Counters* ctr = nullptr;
     // filters
     u32* ns_bitmap = nullptr;
@@ -274,6 +275,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
         delete h;
         return PTE_ERR_CAPACITY;
     }
+    if (const char* ni = getenv("PTE_NO_INVERT")) h->no_invert = atoi(ni) != 0;
     if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
     const char* cfg = getenv("PTE_PASS_CFG");
     if (cfg) h->pass_cfg = std::min(std::max(atoi(cfg), 0), kNumPassCfgs - 1);
@@ -523,8 +525,16 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
                             h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[2], st));
-        CK(h, cudaMemsetAsync(h->bitmap, 0, ((n + 31) / 32) * sizeof(u32), st));
         int grid = (int)std::min<u64>((n + 511) / 512, (u64)h->num_sms * 16);
+        // polarity: flip the bits of the minority (emitted or suppressed), estimated from a sample.  Stream
+        // batches keep the plain polarity (their segment heads depend on the carried state, not on the record).
+        const u64 sample = 4u << 20;
+        diff_sample_kernel<<<(int)std::min<u64>((std::min(n, sample) + 255) / 256, (u64)h->num_sms * 8), 256, 0, st>>>(sorted, n_surv_ptr, h->L, h->ctr, sample);
+        CK(h, cudaGetLastError());
+        bitmap_init_kernel<<<(int)std::min<u64>(((n + 31) / 32 + 255) / 256, (u64)h->num_sms * 8), 256, 0, st>>>(
+            h->bitmap, filtered ? h->keepmap : nullptr, n, h->ctr, (carry || h->no_invert) ? 0 : 1);
+        CK(h, cudaGetLastError());
+        h->n_launches += 2;
         // rounds: each touches a slice of the bitmap small enough to stay in L2
         const u64 bits_per_round = h->diff_round_bytes * 8;
         const u64 drounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);

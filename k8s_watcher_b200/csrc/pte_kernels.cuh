@@ -22,6 +22,9 @@ struct Counters {
     u32 n_pods;
     u32 flags;
     u32 ticket[4];         // tile tickets: [0] intern (filtered runs), [1] radix pass (reset per pass), [2..3] spare
+    u32 sample_emit, sample_total;   // emit fraction of a sample of the sorted records
+    u32 invert;            // 1: the diff stage clears the bits of suppressed records instead of setting emitted ones
+    u32 pad_;
 };
 
 __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo, u64 val_hi, u64 val_lo) {
@@ -295,6 +298,43 @@ __global__ void __launch_bounds__(256) filter_flag_kernel(InternArgs a, u32* __r
 // One launch covers the positions [pos_lo, pos_hi): the host splits the position space into rounds so
 // that the slice of the bitmap a round touches stays resident in L2 (re-reading the records for
 // every round is cheaper than letting the atomics miss).
+// The diff stage is bound by L2 atomics, one per flipped bit.  With uniform phase churn 80 % of the
+// records are emitted; with a quiet cluster almost none are.  So the stage flips the MINORITY: a sample
+// of the sorted records (whole key segments from the front of the array) estimates the emit fraction,
+// and if it is above one half the bitmap starts as "every survivor emitted" and the diff clears bits.
+// The estimate only picks the cheaper of two exact procedures; it cannot change the result.
+__global__ void __launch_bounds__(256)
+diff_sample_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, RecLayout L, Counters* __restrict__ ctr, u64 sample) {
+    const u64 n = min(*n_ptr, sample);
+    const u64 diff_mask = (~0ull << L.key_shift()) | 0x3Full;
+    u32 emit = 0, total = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        const u64 cur = in[i], p = i ? in[i - 1] : ~cur;
+        emit += (((p ^ cur) & diff_mask) | ((p | cur) & 0x80ull)) != 0;
+        total++;
+    }
+    emit = __reduce_add_sync(0xffffffffu, emit);
+    total = __reduce_add_sync(0xffffffffu, total);
+    if ((threadIdx.x & 31) == 0 && total) { atomicAdd(&ctr->sample_emit, emit); atomicAdd(&ctr->sample_total, total); }
+}
+
+// Start value of the emit bitmap: zeros, or (inverted) one bit per survivor -- the keep bitmap of a
+// filtered run, else all positions below n.  Also latches the polarity for the diff launches.
+__global__ void __launch_bounds__(256)
+bitmap_init_kernel(u32* __restrict__ bitmap, const u32* __restrict__ keep, u64 n, Counters* __restrict__ ctr, int allow_invert) {
+    const u32 inv = allow_invert && ctr->sample_total && 2ull * ctr->sample_emit > ctr->sample_total;
+    if (blockIdx.x == 0 && threadIdx.x == 0) ctr->invert = inv;
+    const u64 words = (n + 31) / 32;
+    for (u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (u64)gridDim.x * blockDim.x) {
+        u32 v = 0;
+        if (inv) {
+            v = keep ? keep[w] : 0xffffffffu;
+            if (w == words - 1 && (n & 31)) v &= (1u << (n & 31)) - 1;
+        }
+        bitmap[w] = v;
+    }
+}
+
 // CARRY: the dictionary and one state byte per slot (0 = no live phase known, else 1 + effective phase)
 // survive from the previous batches of a stream.  The first record of a key then compares against that
 // state instead of being emitted unconditionally, and the last record of a key leaves the new state.
@@ -312,6 +352,7 @@ diff_flag_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, u32*
     const u32 ks = L.key_shift();
     const u64 diff_mask = (~0ull << ks) | 0x3Full;
     const u64 pos_mask = L.idx_mask() << 8, lo8 = pos_lo << 8, hi8 = pos_hi << 8;
+    const bool invert = ctr->invert != 0;
     u32 tomb = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x * 2;
     // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffles
@@ -343,10 +384,13 @@ diff_flag_kernel(const u64* __restrict__ in, const u64* __restrict__ n_ptr, u32*
                 if (i + k + 1 >= n || (nx >> ks) != (cur >> ks))      // last record of this key in the batch
                     state_new[slot] = (cur & 0x80ull) ? (u8)0 : (u8)(1 + (cur & 0x3F));
             }
-            if (emit && mine) {
+            if (mine) {
                 const u64 pos = pos8 >> 8;
-                atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
-                tomb += (u32)(cur >> 7) & 1u;
+                if (emit) tomb += (u32)(cur >> 7) & 1u;
+                if (emit != invert) {                      // flip the minority's bits only
+                    if (invert) atomicAnd(bitmap + (pos >> 5), ~(1u << (pos & 31)));
+                    else atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
+                }
             }
             p = cur;
         }
