@@ -283,6 +283,12 @@ def main():
                 "peak_source": peak_src, "traffic": d["traffic"], "launches_per_step": d["launches_per_step"],
                 "avg_launch_ms": d["avg_launch_ms"], "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                 "share_of_step": d["share_of_step"], "frac_of_8TBps_nominal": d["achieved"] / 8000.0,
+                # the whole step against its algorithmic bytes and against the compulsory I/O (30 B in + 16 B per emitted record)
+                "step_algorithmic_bytes": sum(v["launches_per_step"] * v["algorithmic_bytes_per_launch"] for v in by_kernel.values()),
+                "step_achieved": sum(v["launches_per_step"] * v["algorithmic_bytes_per_launch"] for v in by_kernel.values()) / (avg["ms_total"] * 1e-3) / 1e9,
+                "step_dram_traffic": (sum(v["launches_per_step"] * v["traffic"] for v in by_kernel.values()) if all(v["traffic"] for v in by_kernel.values()) else None),
+                "compulsory_io_bytes": 30.0 * n_in + 16.0 * n_emit,
+                "compulsory_io_frac": (30.0 * n_in + 16.0 * n_emit) / (avg["ms_total"] * 1e-3) / 1e9 / peak,
                 "note": "ms of intern/diff/assemble are stage times (kernel + its memsets)", "by_kernel": by_kernel}
 
     # ---- end to end through host buffers (rank-local; max over ranks)
