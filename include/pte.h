@@ -18,7 +18,8 @@
  * Replay-log record (one pod-watch event; the fields handle_pod_event reads,
  * pod_watcher.py:162-167,216-217, plus resourceVersion as the order key):
  *   uid_hi,uid_lo  u64,u64  metadata.uid as a 128-bit integer (never 0:0)
- *   rv             u64      metadata.resourceVersion; replay order is ascending rv
+ *   rv             u64      metadata.resourceVersion; replay order is ascending rv, ties by arrival
+ *                           (a log that is not in that order is pre-sorted on the device)
  *   ns_id          u32      metadata.namespace, interned by the host log
  *   phase          u8       PTE_PH_* code (0..62)
  *   type           u8       PTE_T_ADDED / MODIFIED / DELETED (event['type'], :267)
@@ -44,7 +45,8 @@ enum pte_status {
     PTE_ERR_TABLE_FULL = -5,  /* more distinct uids than max_pods */
     PTE_ERR_BAD_EVENT = -6,   /* type not in {0,1,2}, phase > 62 or uid == 0:0 (the reference would crash
                                  on such an object at pod_watcher.py:216) */
-    PTE_ERR_UNORDERED = -7,   /* rv not non-decreasing in arrival order and rv span too wide to pre-sort */
+    PTE_ERR_UNORDERED = -7,   /* rv decreases along arrival order and cannot be pre-sorted: span too wide
+                                 (bits(rv_max - rv_min) + bits(max_events) > 64), or inside a stream batch */
     PTE_ERR_STATE = -8,       /* call out of sequence (e.g. fetch before run) */
     PTE_ERR_NCCL = -9
 };
@@ -63,7 +65,7 @@ typedef struct pte_stats {
     uint64_t n_emitted;     /* notifications (R-trace if dedupe == 0, T-trace otherwise) */
     uint64_t n_tombstones;  /* emitted DELETED events */
     uint64_t n_pods;        /* distinct uids in the dictionary (cumulative over a PTE_RUN_CARRY stream) */
-    uint32_t ordered;       /* 1: rv was non-decreasing in arrival order */
+    uint32_t ordered;       /* 1: rv was non-decreasing in arrival order; 0: the log was pre-sorted by rv */
     uint32_t n_launches;    /* kernels launched by this pte_run */
     float ms_total;         /* device time of this pte_run, CUDA events on the engine stream */
     float ms_intern;        /* filter + uid interning + record packing */

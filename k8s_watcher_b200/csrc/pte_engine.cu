@@ -89,6 +89,11 @@ struct pte_engine {
     u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
     u8 *state_old = nullptr, *state_new = nullptr;           // per dictionary slot: last known phase of the stream
     bool carry_valid = false;                                // dictionary + state hold a stream that can be continued
+    LogColumns shadow{};                                     // rv-ordered copy of an unordered log (allocated on first use)
+    u32* perm = nullptr;                                     // shadow row -> arrival index
+    u64* d_minmax = nullptr;
+    bool in_reorder = false;
+    u32 last_ordered = 1;
     u64 pods_total = 0, stream_last_rv = 0, batch_first_rv = 0, batch_last_rv = 0;
     u32 *lookback = nullptr, *hist = nullptr;
     u64 lookback_words = 0;
@@ -220,8 +225,60 @@ int check_flags(pte_engine* h, u32 flags) {
         FAIL(h, PTE_ERR_BAD_EVENT, "log holds an event with type not in {ADDED,MODIFIED,DELETED}, phase code > 62 or uid 0:0");
     if (flags & kFlagTableFull)
         FAIL(h, PTE_ERR_TABLE_FULL, "more distinct uids than the engine was created for (max_pods)");
-    if (flags & kFlagUnordered)
-        FAIL(h, PTE_ERR_UNORDERED, "resourceVersion decreases along arrival order; sort the log by rv before ingest");
+    return PTE_OK;
+}
+
+// Bring a log whose rv decreases somewhere into replay order (ascending rv, ties by arrival) in shadow
+// columns, run the pipeline on those, map the emitted indices back to arrival indices.
+int run_reordered(pte_engine* h, int flags, pte_stats* out) {
+    const u64 n = h->n_events, c = h->cap_ev;
+    cudaStream_t st = h->stream;
+    if (!h->d_minmax) CK(h, cudaMalloc((void**)&h->d_minmax, 2 * sizeof(u64)));
+    const u64 init[2] = {~0ull, 0ull};
+    CK(h, cudaMemcpyAsync(h->d_minmax, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+    rv_minmax_kernel<<<grid, 256, 0, st>>>(h->rv, n, h->d_minmax);
+    CK(h, cudaGetLastError());
+    u64 mm[2];
+    CK(h, cudaMemcpyAsync(mm, h->d_minmax, sizeof(mm), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    const u32 span_bits = std::max<u32>(1, bitlen_host(mm[1] - mm[0]));
+    if (span_bits + h->L.idx_bits > 64)
+        FAIL(h, PTE_ERR_UNORDERED, "resourceVersion decreases along arrival order and its span is too wide to pre-sort "
+                                   "(bits(rv_max - rv_min) + bits(max_events) > 64): sort the log by rv before ingest");
+    if (!h->perm) {
+        if (dev_alloc(h, &h->shadow.uid_hi, c) || dev_alloc(h, &h->shadow.uid_lo, c) || dev_alloc(h, &h->shadow.rv, c) ||
+            dev_alloc(h, &h->shadow.ns, c) || dev_alloc(h, &h->shadow.phase, c) || dev_alloc(h, &h->shadow.type, c) ||
+            dev_alloc(h, &h->perm, c))
+            return PTE_ERR_CUDA;
+        CK(h, cudaMemsetAsync(h->shadow.rv, 0, c * sizeof(u64), st));
+    }
+    rv_pack_kernel<<<grid, 256, 0, st>>>(h->rv, n, mm[0], h->L.idx_bits, h->recA);
+    CK(h, cudaGetLastError());
+    u64* sorted = nullptr;
+    h->pass_ev_used = 0;
+    int rc = sort_field(h, h->recA, h->recB, h->recC, nullptr, n, (int)h->L.idx_bits, (int)(h->L.idx_bits + span_bits), &sorted);
+    if (rc) return rc;
+    LogColumns src{h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type};
+    permute_log_kernel<<<grid, 256, 0, st>>>(sorted, n, h->L.idx_mask(), src, h->shadow, h->perm);
+    CK(h, cudaGetLastError());
+    // run on the shadow columns
+    std::swap(h->uid_hi, h->shadow.uid_hi); std::swap(h->uid_lo, h->shadow.uid_lo); std::swap(h->rv, h->shadow.rv);
+    std::swap(h->ns, h->shadow.ns); std::swap(h->phase, h->shadow.phase); std::swap(h->type, h->shadow.type);
+    h->in_reorder = true;
+    rc = pte_run(h, flags, out);
+    h->in_reorder = false;
+    std::swap(h->uid_hi, h->shadow.uid_hi); std::swap(h->uid_lo, h->shadow.uid_lo); std::swap(h->rv, h->shadow.rv);
+    std::swap(h->ns, h->shadow.ns); std::swap(h->phase, h->shadow.phase); std::swap(h->type, h->shadow.type);
+    if (rc) return rc;
+    if (h->last.n_emitted) {
+        grid = (int)std::min<u64>((h->last.n_emitted + 255) / 256, (u64)h->num_sms * 16);
+        map_idx_kernel<<<grid, 256, 0, st>>>(h->out_idx, h->ctr, h->perm);
+        CK(h, cudaGetLastError());
+        CK(h, cudaStreamSynchronize(st));
+    }
+    h->last_ordered = 0;
+    if (out) out->ordered = 0;
     return PTE_OK;
 }
 
@@ -243,7 +300,8 @@ void pte_destroy(pte_handle h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
-                    h->out_type, h->d_counts_send, h->d_counts_recv};
+                    h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
+                    h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
@@ -575,6 +633,13 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     CK(h, cudaStreamSynchronize(st));
     int rc = check_flags(h, h->last.flags);
     if (rc) { h->carry_valid = false; return rc; }
+    if (h->last.flags & kFlagUnordered) {
+        h->carry_valid = false;
+        if (carry) FAIL(h, PTE_ERR_UNORDERED, "resourceVersion decreases inside a stream batch: batches of a stream must be rv-ordered");
+        if (h->in_reorder) FAIL(h, PTE_ERR_UNORDERED, "internal: the rv pre-sort did not order the log");
+        return run_reordered(h, flags, out);
+    }
+    h->last_ordered = 1;
     h->pods_total += h->last.n_pods;
     if (carry) { std::swap(h->state_old, h->state_new); h->stream_last_rv = n ? h->batch_last_rv : h->stream_last_rv; }
     h->carry_valid = carry;

@@ -542,6 +542,49 @@ digest_kernel(const u32* __restrict__ out_idx, const u8* __restrict__ out_phase,
     if ((threadIdx.x & 31) == 0 && acc) atomicAdd(&ctr->digest, acc);
 }
 
+// ---- logs that are not in resourceVersion order -------------------------------------------------
+// Replay order is ascending rv (ties: arrival).  Such a log is brought into that order once: records
+// (rv - rv_min, arrival index) go through the same radix sort, the columns are gathered into shadow
+// buffers in sorted order, the normal pipeline runs on those, and the emitted indices are mapped back.
+__global__ void __launch_bounds__(256) rv_minmax_kernel(const u64* __restrict__ rv, u64 n, u64* __restrict__ mm) {
+    u64 lo = ~0ull, hi = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        const u64 v = rv[i];
+        lo = min(lo, v); hi = max(hi, v);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(mm, lo); atomicMax(mm + 1, hi); }
+}
+
+__global__ void __launch_bounds__(256)
+rv_pack_kernel(const u64* __restrict__ rv, u64 n, u64 rv_min, u32 idx_bits, u64* __restrict__ rec) {
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        rec[i] = ((rv[i] - rv_min) << idx_bits) | i;
+}
+
+struct LogColumns { u64 *uid_hi, *uid_lo, *rv; u32* ns; u8 *phase, *type; };
+
+__global__ void __launch_bounds__(256)
+permute_log_kernel(const u64* __restrict__ sorted, u64 n, u64 idx_mask, LogColumns src, LogColumns dst, u32* __restrict__ perm) {
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
+        const u64 i = sorted[j] & idx_mask;
+        perm[j] = (u32)i;
+        dst.uid_hi[j] = src.uid_hi[i]; dst.uid_lo[j] = src.uid_lo[i]; dst.rv[j] = src.rv[i];
+        dst.ns[j] = src.ns[i]; dst.phase[j] = src.phase[i]; dst.type[j] = src.type[i];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+map_idx_kernel(u32* __restrict__ out_idx, const Counters* __restrict__ ctr, const u32* __restrict__ perm) {
+    const u64 n = ctr->n_emitted;
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x)
+        out_idx[j] = perm[out_idx[j]];
+}
+
 // ---- synthetic replay log -----------------------------------------------------
 struct GenArgs {
     GenParams g;

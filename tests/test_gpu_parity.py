@@ -239,12 +239,52 @@ def test_zero_uid_is_rejected(eng):
     assert ei.value.code == -6
 
 
-def test_unordered_log_is_rejected(eng):
+@pytest.mark.parametrize("env", list(FILTERS))
+@pytest.mark.parametrize("dedupe", [True, False])
+def test_unordered_log_replays_in_rv_order(eng, env, dedupe):
+    """Replay order is ascending rv (ties: arrival order); a shuffled log gives the same notifications."""
+    n, pods = 150_000, 2_000
+    cols = c_oracle.generate(SEED + 9, n, pods, dist=1, p_del=0.07, p_nostatus=0.03, p_null=0.03)
+    rng = np.random.default_rng(4)
+    perm = rng.permutation(n)
+    shuf = {k: v[perm] for k, v in cols.items()}
+    st = check_against_oracle(eng, shuf, FILTERS[env], dedupe, pods)      # the oracle sorts by (rv, arrival) itself
+    assert st["ordered"] == 0
+    # ... and in terms of the ordered log: the same events, in the same order
+    got = eng.fetch(columns=("idx",)).idx.astype(np.int64)
+    want, _, _ = c_oracle.replay(cols, critical_only=FILTERS[env]["critical_only"], ns_allow=FILTERS[env]["ns_allow"],
+                                 dedupe=dedupe, pods_hint=pods)
+    assert np.array_equal(perm[got], want.astype(np.int64))
+    # the engine's copy of the log is untouched
+    back = eng.read_log()
+    assert all(np.array_equal(back[k], shuf[k]) for k in shuf)
+
+
+def test_unordered_log_with_rv_ties_and_offset(eng):
+    n = 40_000
+    cols = c_oracle.generate(21, n, 300, p_del=0.1)
+    cols["rv"] = (cols["rv"] // np.uint64(7)) + np.uint64(1 << 40)       # ties, far from zero
+    perm = np.random.default_rng(8).permutation(n)
+    shuf = {k: v[perm] for k, v in cols.items()}
+    check_against_oracle(eng, shuf, FILTERS["staging"], True, 300)
+
+
+def test_unordered_log_with_too_wide_rv_span_is_rejected(eng):
+    cols = c_oracle.generate(9, 5000, 10)
+    cols["rv"][100] = np.uint64(1) << np.uint64(63)
+    eng.set_filters(None)
+    eng.ingest(cols)
+    with pytest.raises(PteError) as ei:
+        eng.run()
+    assert ei.value.code == -7 and "span" in str(ei.value)
+
+
+def test_unordered_stream_batch_is_rejected(eng):
     cols = c_oracle.generate(9, 5000, 10)
     cols["rv"][[100, 4000]] = cols["rv"][[4000, 100]]
     eng.ingest(cols)
     with pytest.raises(PteError) as ei:
-        eng.run()
+        eng.run(carry=True)
     assert ei.value.code == -7
 
 
