@@ -154,6 +154,19 @@ int pte_run(pte_handle h, int flags, pte_stats* out);
 int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t* ns_id,
               uint8_t* phase, uint8_t* type, uint64_t cap, uint64_t* n_out);
 
+/* The request bodies the reference would POST for emitted records [first, first + count) of the last pte_run:
+ * json.dumps(_extract_pod_data(pod) + event_type) (pod_watcher.py:159-202, :233; clusterapi_client.py:36),
+ * for pods that carry only what a replay-log row holds (name "pod-" + uid[:13], no labels, containers, ...).
+ * The JSON text around the per-record fields is given by the caller as ready-made fragments, so nothing has
+ * to be escaped on the device: blob holds 6 segments, then 3 event-type fragments, n_phase phase fragments
+ * (by PTE_PH_* code) and n_ns namespace fragments (by ns_id), back to back; fragment i is
+ * blob[frag_off[i], frag_off[i+1]).  A body is  seg0 uid[:13] seg1 NS seg2 uid seg3 PHASE seg4 TYPE seg5.
+ * out receives the bodies back to back, offsets[0..count] their start (offsets[count] = total bytes);
+ * with out == NULL only *n_bytes (the size needed) is computed. */
+int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const char* blob, uint32_t blob_len,
+                           const uint32_t* frag_off, uint32_t n_phase, uint32_t n_ns, char* out, uint64_t out_cap,
+                           uint64_t* offsets, uint64_t* n_bytes);
+
 /* Order-sensitive 64-bit digest of the emitted records (position, rv, uid, ns, phase, type);
  * same arithmetic as oracle/oracle.c rec_digest.  For parity at sizes too big to compare in full. */
 int pte_digest(pte_handle h, uint64_t* out);

@@ -59,6 +59,8 @@ SYMBOLS = {
     "pte_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PteStats)]),
     "pte_fetch": (C.c_int, [C.c_void_p, _u32p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, _u64p]),
     "pte_digest": (C.c_int, [C.c_void_p, _u64p]),
+    "pte_serialize_payloads": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint32, _u32p, C.c_uint32,
+                                         C.c_uint32, C.c_void_p, C.c_uint64, _u64p, _u64p]),
     "pte_host_alloc": (C.c_void_p, [C.c_size_t]),
     "pte_host_free": (None, [C.c_void_p]),
     "pte_shard_of": (C.c_uint32, [C.c_uint64, C.c_uint64, C.c_uint32]),

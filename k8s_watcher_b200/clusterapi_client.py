@@ -102,9 +102,10 @@ class ClusterApiClient:
     def update_pod_status_batch(self, batch, event_timestamp: Optional[str] = None) -> int:
         """Hand every emitted record of ``batch`` to the sink, in replay order.
         Returns the number of successful updates."""
+        endpoint = "%s/api/pods/update" % self.base_url
         ok = 0
-        for payload in batch.payloads(event_timestamp=event_timestamp):
-            ok += bool(self.update_pod_status(payload))
+        for body in batch.wire_bodies(event_timestamp=event_timestamp):      # serialised in bulk (on the GPU for column logs)
+            ok += self._post_body(endpoint, body, "batch")
         return ok
 
     def health_check(self) -> bool:

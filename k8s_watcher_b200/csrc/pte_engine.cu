@@ -91,6 +91,10 @@ struct pte_engine {
     bool carry_valid = false;                                // dictionary + state hold a stream that can be continued
     LogColumns shadow{};                                     // rv-ordered copy of an unordered log (allocated on first use)
     u32* perm = nullptr;                                     // shadow row -> arrival index
+    char *pay_buf = nullptr, *pay_blob = nullptr;            // serialised payloads; JSON fragments
+    u64 pay_buf_cap = 0, pay_blob_cap = 0, pay_off_cap = 0, pay_tile_cap = 0;
+    u32* pay_frag_off = nullptr; u64 pay_frag_cap = 0;
+    u64 *pay_rec_off = nullptr, *pay_tile_off = nullptr;
     u64* d_minmax = nullptr;
     bool in_reorder = false;
     u32 last_ordered = 1;
@@ -220,6 +224,16 @@ int dev_alloc(pte_engine* h, T** p, u64 count) {
     return PTE_OK;
 }
 
+// (re)allocate a device buffer that only ever grows
+template <typename T>
+int grow(pte_engine* h, T** p, u64* cap, u64 need) {
+    if (*cap >= need) return PTE_OK;
+    if (*p) { CK(h, cudaFree(*p)); *p = nullptr; *cap = 0; }
+    CK(h, cudaMalloc((void**)p, need * sizeof(T)));
+    *cap = need;
+    return PTE_OK;
+}
+
 int check_flags(pte_engine* h, u32 flags) {
     if (flags & kFlagBadEvent)
         FAIL(h, PTE_ERR_BAD_EVENT, "log holds an event with type not in {ADDED,MODIFIED,DELETED}, phase code > 62 or uid 0:0");
@@ -301,7 +315,8 @@ void pte_destroy(pte_handle h) {
     void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
-                    h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax};
+                    h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
+                    h->pay_frag_off, h->pay_rec_off, h->pay_tile_off};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
@@ -714,6 +729,51 @@ int pte_digest(pte_handle h, uint64_t* out) {
     CK(h, cudaMemcpyAsync(&d, &h->ctr->digest, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
     *out = d;
+    return PTE_OK;
+}
+
+int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const char* blob, uint32_t blob_len,
+                           const uint32_t* frag_off, uint32_t n_phase, uint32_t n_ns, char* out, uint64_t out_cap,
+                           uint64_t* offsets, uint64_t* n_bytes) {
+    if (!h || !blob || !frag_off || !n_bytes) FAIL(h, PTE_ERR_INVALID, "NULL argument");
+    if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_serialize_payloads before a successful pte_run");
+    if (first > h->last.n_emitted || count > h->last.n_emitted - first) FAIL(h, PTE_ERR_INVALID, "record range outside the emitted records");
+    if (n_phase == 0 || n_ns == 0) FAIL(h, PTE_ERR_INVALID, "empty phase or namespace table");
+    *n_bytes = 0;
+    if (count == 0) { if (offsets) offsets[0] = 0; return PTE_OK; }
+    CK(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    const u64 n_frag = 9ull + n_phase + n_ns;
+    if (frag_off[n_frag] != blob_len) FAIL(h, PTE_ERR_INVALID, "fragment offsets do not end at blob_len");
+    int rc;
+    if ((rc = grow(h, &h->pay_blob, &h->pay_blob_cap, (u64)blob_len + 16))) return rc;
+    if ((rc = grow(h, &h->pay_frag_off, &h->pay_frag_cap, n_frag + 1))) return rc;
+    const u64 tiles = (count + kPayTile - 1) / kPayTile;
+    if ((rc = grow(h, &h->pay_tile_off, &h->pay_tile_cap, tiles + 1))) return rc;
+    if ((rc = grow(h, &h->pay_rec_off, &h->pay_off_cap, count + 1))) return rc;
+    if (tiles > h->lookback_words) FAIL(h, PTE_ERR_CAPACITY, "too many records in one call");
+    CK(h, cudaMemcpyAsync(h->pay_blob, blob, blob_len, cudaMemcpyHostToDevice, st));
+    CK(h, cudaMemcpyAsync(h->pay_frag_off, frag_off, (n_frag + 1) * sizeof(u32), cudaMemcpyHostToDevice, st));
+    PayloadTable t{h->pay_blob, h->pay_frag_off, n_phase, n_ns};
+    int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
+    payload_len_kernel<<<grid, 256, 0, st>>>(t, h->out_ns, h->out_phase, h->out_type, first, count, h->lookback);
+    CK(h, cudaGetLastError());
+    scan_u32_to_u64_kernel<<<1, 1024, 0, st>>>(h->lookback, tiles, h->pay_tile_off);
+    CK(h, cudaGetLastError());
+    u64 total = 0;
+    CK(h, cudaMemcpyAsync(&total, h->pay_tile_off + tiles, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    *n_bytes = total;
+    if (!out || !offsets) return PTE_OK;                       // size query
+    if (total > out_cap) FAIL(h, PTE_ERR_CAPACITY, "output buffer smaller than the serialised payloads (size in *n_bytes)");
+    if ((rc = grow(h, &h->pay_buf, &h->pay_buf_cap, total + 64))) return rc;
+    payload_write_kernel<<<grid, 256, 0, st>>>(t, h->out_idx, h->out_ns, h->out_phase, h->out_type, h->uid_hi, h->uid_lo,
+                                                first, count, h->pay_tile_off, h->pay_buf, h->pay_rec_off);
+    CK(h, cudaGetLastError());
+    CK(h, cudaMemcpyAsync(out, h->pay_buf, total, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(offsets, h->pay_rec_off, count * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    offsets[count] = total;
     return PTE_OK;
 }
 

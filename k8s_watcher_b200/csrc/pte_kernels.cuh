@@ -542,6 +542,131 @@ digest_kernel(const u32* __restrict__ out_idx, const u8* __restrict__ out_phase,
     if ((threadIdx.x & 31) == 0 && acc) atomicAdd(&ctr->digest, acc);
 }
 
+// ---- payload serialisation ------------------------------------------------------------------------
+// The JSON body the reference would POST for an emitted record of a column log
+// (json.dumps(_extract_pod_data(pod) + event_type), pod_watcher.py:159-202,:233; clusterapi_client.py:36).
+// Everything that needs escaping is prepared by the host as ready-made JSON fragments; a record is
+//   seg0 uid[:13] seg1 NS seg2 uid seg3 PHASE seg4 TYPE seg5
+// with NS / PHASE / TYPE looked up by code.  One kernel sizes the records, the tile sums are scanned,
+// and one warp per record then copies the fragments and formats the uid.
+struct PayloadTable {
+    const char* blob;      // all fragments, back to back
+    const u32* off;        // fragment i = blob[off[i], off[i+1]):  6 segments, 3 types, n_phase phases, n_ns namespaces
+    u32 n_phase, n_ns;
+    __device__ __forceinline__ u32 len(u32 i) const { return off[i + 1] - off[i]; }
+    __device__ __forceinline__ u32 type_frag(u32 t) const { return 6 + t; }
+    __device__ __forceinline__ u32 phase_frag(u32 p) const { return 9 + min(p, n_phase - 1); }
+    __device__ __forceinline__ u32 ns_frag(u32 n) const { return 9 + n_phase + min(n, n_ns - 1); }
+};
+static constexpr int kPayTile = 1024;      // records per scan tile
+
+__device__ __forceinline__ u32 payload_len(const PayloadTable& t, u32 fixed, u32 ns, u32 ph, u32 ty) {
+    return fixed + 13 + 36 + t.len(t.ns_frag(ns)) + t.len(t.phase_frag(ph)) + t.len(t.type_frag(ty));
+}
+
+__global__ void __launch_bounds__(256)
+payload_len_kernel(PayloadTable t, const u32* __restrict__ ns, const u8* __restrict__ phase, const u8* __restrict__ type,
+                   u64 first, u64 count, u32* __restrict__ tile_sum) {
+    __shared__ u32 s_w[8];
+    u32 fixed = 0;
+    for (int k = 0; k < 6; k++) fixed += t.len(k);
+    const u64 n_tiles = (count + kPayTile - 1) / kPayTile;
+    for (u64 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        u32 sum = 0;
+        for (u32 k = threadIdx.x; k < kPayTile; k += 256) {
+            const u64 j = tile * kPayTile + k;
+            if (j < count) sum += payload_len(t, fixed, ns[first + j], phase[first + j], type[first + j]);
+        }
+        sum = __reduce_add_sync(0xffffffffu, sum);
+        if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            u32 v = 0;
+            for (int k = 0; k < 8; k++) v += s_w[k];
+            tile_sum[tile] = v;
+        }
+        __syncthreads();
+    }
+}
+
+// exclusive scan of n 32-bit tile sums by one block -> 64-bit offsets (n + 1 entries)
+__global__ void __launch_bounds__(1024) scan_u32_to_u64_kernel(const u32* __restrict__ in, u64 n, u64* __restrict__ out) {
+    __shared__ u64 s_part[1024];
+    const u64 per = (n + 1023) / 1024;
+    const u64 lo = min(n, threadIdx.x * per), hi = min(n, lo + per);
+    u64 sum = 0;
+    for (u64 i = lo; i < hi; i++) sum += in[i];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u64 run = 0;
+        for (int k = 0; k < 1024; k++) { u64 v = s_part[k]; s_part[k] = run; run += v; }
+        out[n] = run;
+    }
+    __syncthreads();
+    u64 run = s_part[threadIdx.x];
+    for (u64 i = lo; i < hi; i++) { out[i] = run; run += in[i]; }
+}
+
+__device__ __forceinline__ void warp_copy(char* __restrict__ dst, const char* __restrict__ src, u32 len, u32 lane) {
+    for (u32 k = lane; k < len; k += 32) dst[k] = src[k];
+}
+__device__ __forceinline__ char uid_char(u64 hi, u64 lo, u32 pos) {      // pos in the 8-4-4-4-12 text form
+    if (pos == 8 || pos == 13 || pos == 18 || pos == 23) return '-';
+    const u32 nib = pos - (pos > 8) - (pos > 13) - (pos > 18) - (pos > 23);      // 0..31, most significant first
+    const u64 w = nib < 16 ? hi : lo;
+    const u32 v = (u32)(w >> (60 - 4 * (nib & 15))) & 15u;
+    return (char)(v < 10 ? '0' + v : 'a' + v - 10);
+}
+
+__global__ void __launch_bounds__(256)
+payload_write_kernel(PayloadTable t, const u32* __restrict__ out_idx, const u32* __restrict__ ns, const u8* __restrict__ phase,
+                     const u8* __restrict__ type, const u64* __restrict__ uid_hi, const u64* __restrict__ uid_lo,
+                     u64 first, u64 count, const u64* __restrict__ tile_off, char* __restrict__ out, u64* __restrict__ rec_off) {
+    __shared__ u32 s_len[kPayTile];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u32 fixed = 0;
+    for (int k = 0; k < 6; k++) fixed += t.len(k);
+    const u64 n_tiles = (count + kPayTile - 1) / kPayTile;
+    for (u64 tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (u32 k = threadIdx.x; k < kPayTile; k += 256) {
+            const u64 j = tile * kPayTile + k;
+            s_len[k] = j < count ? payload_len(t, fixed, ns[first + j], phase[first + j], type[first + j]) : 0u;
+        }
+        __syncthreads();
+        // each warp owns 128 consecutive records of the tile: running offset inside the warp's slice
+        u64 base = tile_off[tile];
+        for (u32 k = 0; k < warp * 128; k += 32) base += __reduce_add_sync(0xffffffffu, s_len[k + lane]);
+        for (u32 r = 0; r < 128; r++) {
+            const u32 k = warp * 128 + r;
+            const u64 j = tile * kPayTile + k;
+            if (j >= count) break;
+            const u64 e = first + j;
+            if (lane == 0) rec_off[j] = base;
+            char* d = out + base;
+            const u32 i = out_idx[e];
+            const u64 hi = uid_hi[i], lo = uid_lo[i];
+            u32 o = 0, f;
+            warp_copy(d + o, t.blob + t.off[0], t.len(0), lane); o += t.len(0);
+            if (lane < 13) d[o + lane] = uid_char(hi, lo, lane);
+            o += 13;
+            warp_copy(d + o, t.blob + t.off[1], t.len(1), lane); o += t.len(1);
+            f = t.ns_frag(ns[e]); warp_copy(d + o, t.blob + t.off[f], t.len(f), lane); o += t.len(f);
+            warp_copy(d + o, t.blob + t.off[2], t.len(2), lane); o += t.len(2);
+            d[o + lane] = uid_char(hi, lo, lane);
+            if (lane < 4) d[o + 32 + lane] = uid_char(hi, lo, 32 + lane);
+            o += 36;
+            warp_copy(d + o, t.blob + t.off[3], t.len(3), lane); o += t.len(3);
+            f = t.phase_frag(phase[e]); warp_copy(d + o, t.blob + t.off[f], t.len(f), lane); o += t.len(f);
+            warp_copy(d + o, t.blob + t.off[4], t.len(4), lane); o += t.len(4);
+            f = t.type_frag(type[e]); warp_copy(d + o, t.blob + t.off[f], t.len(f), lane); o += t.len(f);
+            warp_copy(d + o, t.blob + t.off[5], t.len(5), lane);
+            base += s_len[k];
+        }
+        __syncthreads();
+    }
+}
+
 // ---- logs that are not in resourceVersion order -------------------------------------------------
 // Replay order is ascending rv (ties: arrival).  Such a log is brought into that order once: records
 // (rv - rv_min, arrival index) go through the same radix sort, the columns are gathered into shadow

@@ -207,6 +207,27 @@ class PhaseTransitionEngine:
         z = {name: (np.empty(0, dts[name]) if a is None else a[:k]) for name, a in out.items()}
         return EmittedColumns(**z)
 
+    def serialize_payloads(self, fragments: Sequence[bytes], n_phase: int, n_ns: int, first: int = 0,
+                           count: Optional[int] = None):
+        """Request bodies of emitted records [first, first+count) built on the device (pte_serialize_payloads).
+        ``fragments`` = 6 segments + 3 event types + n_phase phases + n_ns namespaces, each ready-made JSON text.
+        Returns (bytes buffer as uint8 array, offsets uint64[count+1])."""
+        n = int(self.last_stats["n_emitted"]) if self.last_stats else 0
+        count = n - first if count is None else count
+        assert len(fragments) == 9 + n_phase + n_ns
+        off = np.zeros(len(fragments) + 1, np.uint32)
+        off[1:] = np.cumsum([len(f) for f in fragments])
+        blob = b"".join(fragments)
+        need = C.c_uint64()
+        self._ck(self._L.pte_serialize_payloads(self._h, first, count, blob, len(blob), _ptr(off, C.c_uint32), n_phase, n_ns,
+                                                None, 0, None, C.byref(need)))
+        out = np.empty(max(int(need.value), 1), np.uint8)
+        offsets = np.zeros(count + 1, np.uint64)
+        self._ck(self._L.pte_serialize_payloads(self._h, first, count, blob, len(blob), _ptr(off, C.c_uint32), n_phase, n_ns,
+                                                out.ctypes.data_as(C.c_void_p), out.shape[0], _ptr(offsets, C.c_uint64),
+                                                C.byref(need)))
+        return out[: int(need.value)], offsets
+
     def digest(self) -> int:
         d = C.c_uint64()
         self._ck(self._L.pte_digest(self._h, C.byref(d)))

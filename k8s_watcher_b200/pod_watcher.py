@@ -52,6 +52,19 @@ class Batch:
         """Arrival indices (into the log) of the emitted events."""
         return self.emitted.idx
 
+    def wire_bodies(self, event_timestamp: Optional[str] = None) -> List[bytes]:
+        """The request bodies of all notifications, as ``requests`` would send them.  For a column log
+        (rows only, no pod objects) they are serialised on the device in one call; otherwise per payload."""
+        ts = event_timestamp if event_timestamp is not None else datetime.now().isoformat()
+        eng = self.watcher._engine
+        if self.log._pods is None and eng is not None and self is self.watcher.batches[-1] and len(self):
+            frags, n_phase, n_ns = payload_fragments(self.watcher, self.log, ts)
+            buf, off = eng.serialize_payloads(frags, n_phase, n_ns)
+            raw = buf.tobytes()
+            return [raw[int(off[i]):int(off[i + 1])] for i in range(len(self))]
+        import json
+        return [json.dumps(p, allow_nan=False).encode("utf-8") for p in self.payloads(event_timestamp=ts)]
+
     def payloads(self, event_timestamp: Optional[str] = None) -> Iterator[Dict[str, Any]]:
         """Payload dicts exactly as the reference builds them at pod_watcher.py:232-233,
         one per emitted record.  ``event_timestamp`` pins the wall-clock field (:199)."""
@@ -59,6 +72,48 @@ class Batch:
             d = self.watcher._extract_pod_data(self.log.pod_at(i), event_timestamp=event_timestamp)
             d["event_type"] = codes.TYPE_NAMES[t]
             yield d
+
+
+def payload_fragments(watcher: "PodWatcher", log: ReplayLog, event_timestamp: str):
+    """JSON text around the per-record fields of a column log's request body, for pte_serialize_payloads.
+
+    Derived from json.dumps of a sample payload with placeholders, so key order, separators and escaping
+    are whatever the reference's ``session.post(json=...)`` produces (clusterapi_client.py:36).
+    Returns (fragments, n_phase, n_ns)."""
+    import json
+    marks = {k: "\u0000%s\u0000" % k for k in ("NAME", "NS", "UID", "PHASE", "TYPE")}
+
+    class _P:  # a pod whose per-record fields are placeholders
+        pass
+    pod = log.pod_at(0) if len(log) else None
+    md = type("M", (), dict(name="pod-" + marks["NAME"], namespace=marks["NS"], uid=marks["UID"], labels=None,
+                            annotations=None, creation_timestamp=None))()
+    st = type("S", (), dict(phase=marks["PHASE"], conditions=None, container_statuses=None))()
+    sample = watcher._extract_pod_data(type("P", (), dict(metadata=md, status=st, spec=None))(),
+                                       event_timestamp=event_timestamp)
+    sample["event_type"] = marks["TYPE"]
+    text = json.dumps(sample, allow_nan=False)
+    # split at the (escaped) placeholders; quotes around NS / PHASE / TYPE belong to the fragment tables
+    def esc(m):
+        return json.dumps(m)[1:-1]
+    parts, rest = [], text
+    for key, with_quotes in (("NAME", False), ("NS", True), ("UID", False), ("PHASE", True), ("TYPE", True)):
+        token = ('"%s"' % esc(marks[key])) if with_quotes else esc(marks[key])
+        head, rest = rest.split(token, 1)
+        parts.append(head)
+    parts.append(rest)
+    segs = [p.encode("utf-8") for p in parts]
+    types = [json.dumps(t).encode() for t in codes.TYPE_NAMES]
+    phases = []
+    for code in range(max(len(log.phases), codes.PH_NOSTATUS + 1)):
+        if code == codes.PH_NOSTATUS:
+            phases.append(b'"Unknown"')                       # pod.status is None (pod_watcher.py:167)
+        elif code == codes.PH_NULL or code >= len(log.phases) or log.phases[code] is None:
+            phases.append(b"null")
+        else:
+            phases.append(json.dumps(log.phases[code]).encode())
+    nss = [json.dumps(n).encode() for n in log.namespaces] or [b'""']
+    return segs + types + phases + nss, len(phases), len(nss)
 
 
 class PodWatcher:

@@ -419,3 +419,32 @@ def test_live_loop_micro_batches_match_one_replay(monkeypatch):
         want = dict(fx["payloads"][k])
         b.pop("event_timestamp"), want.pop("event_timestamp")
         assert b == want
+
+
+# ---- payload serialisation on the device ------------------------------------------
+def test_device_wire_bodies_match_requests_bytes(monkeypatch):
+    from k8s_watcher_b200 import ClusterApiClient
+    from k8s_watcher_b200.clusterapi_client import wire_body
+    monkeypatch.chdir(ROOT)
+    log = ReplayLog.synthetic(SEED, 60_000, 700, dist=1, p_del=0.1, p_nostatus=0.05, p_null=0.05)
+    log.namespaces = ['de"fault', "kube\\system", "prodüction", "monitoring", "other"]
+    sink = ClusterApiClient("http://clusterapi.invalid")
+    w = PodWatcher("production", sink=sink)          # production filters: namespace list + critical-only
+    w.config["watcher"]["namespaces"] = ['de"fault', "prodüction", "monitoring", "kube\\system"]
+    batch = w.replay(log)
+    ts = "2025-06-01T12:00:00"
+    got = batch.wire_bodies(event_timestamp=ts)
+    want = [wire_body(p) for p in batch.payloads(event_timestamp=ts)]
+    assert len(got) == len(want) == len(batch) > 1000
+    assert got == want
+    # the sink takes the whole batch in one call and sees the same bytes
+    assert sink.update_pod_status_batch(batch, event_timestamp=ts) == len(batch)
+    assert sink.transport.bodies() == want
+    # a sub-range, and an empty batch
+    from k8s_watcher_b200.pod_watcher import payload_fragments
+    frags, n_phase, n_ns = payload_fragments(w, log, ts)
+    buf, off = w._engine.serialize_payloads(frags, n_phase, n_ns, first=1500, count=1100)
+    raw = buf.tobytes()
+    assert [raw[int(off[i]):int(off[i + 1])] for i in range(1100)] == want[1500:2600]
+    empty = w.replay(ReplayLog.synthetic(1, 0, 1))
+    assert empty.wire_bodies(event_timestamp=ts) == []

@@ -207,3 +207,24 @@ def test_sink_contract():
         assert cl.update_pod_status({"name": "p"}) is False and cl.health_check() is False
     assert c.update_pod_status({"bad": float("nan")}) is False       # allow_nan=False, never raises
     assert wire_body({"a": 1, "b": [1, {"c": None}]}) == json.dumps({"a": 1, "b": [1, {"c": None}]}).encode()
+
+
+def test_payload_fragments_rebuild_the_reference_wire_body(in_root):
+    """The fragments handed to pte_serialize_payloads, glued together the way the kernel does it, are
+    byte-identical to json.dumps of the payload -- including names that need escaping."""
+    from k8s_watcher_b200.pod_watcher import payload_fragments
+    log = ReplayLog.synthetic(4, 400, 9, p_del=0.2, p_nostatus=0.2, p_null=0.2)
+    log.namespaces = ['de"fault', "kube\\system", "prodüction", "monitoring\n", "other"]
+    w = PodWatcher("staging")
+    w.environment = 'st"agingé'
+    frags, n_phase, n_ns = payload_fragments(w, log, "2025-01-01T00:00:00")
+    segs, types, phases, nss = frags[:6], frags[6:9], frags[9:9 + n_phase], frags[9 + n_phase:]
+    assert len(nss) == n_ns == 5 and n_phase >= 7
+    for i in range(len(log)):
+        c = log.columns
+        uid = codes.uid_to_str(c["uid_hi"][i], c["uid_lo"][i]).encode()
+        body = (segs[0] + uid[:13] + segs[1] + nss[int(c["ns_id"][i])] + segs[2] + uid + segs[3] +
+                phases[int(c["phase"][i])] + segs[4] + types[int(c["type"][i])] + segs[5])
+        want = w._extract_pod_data(log.pod_at(i), event_timestamp="2025-01-01T00:00:00")
+        want["event_type"] = log.type_at(i)
+        assert body == wire_body(want)
