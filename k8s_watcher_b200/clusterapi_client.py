@@ -59,9 +59,19 @@ def wire_body(pod_data: Dict[str, Any]) -> bytes:
 
 
 class ClusterApiClient:
-    def __init__(self, base_url: str, api_key: Optional[str] = None, *, transport: Optional[Callable] = None):
+    def __init__(self, base_url: str, api_key: Optional[str] = None, *, transport: Optional[Callable] = None,
+                 timeout: Optional[float] = None, max_attempts: int = 1, delay_seconds: float = 0.0,
+                 sleep: Callable[[float], None] = None):
+        """``timeout``, ``max_attempts`` and ``delay_seconds`` are the knobs the reference's config declares
+        (config/base.yaml: clusterapi.timeout, clusterapi.retry.*) but its code never reads; the defaults keep
+        the reference's behaviour (one attempt, no timeout).  See :meth:`from_config`."""
         self.base_url = base_url.rstrip("/")
         self.api_key = api_key
+        self.timeout = timeout
+        self.max_attempts = max(1, int(max_attempts))
+        self.delay_seconds = float(delay_seconds)
+        import time as _time
+        self._sleep = sleep if sleep is not None else _time.sleep
         self.transport = transport if transport is not None else MockTransport()
         self.session = self.transport            # the reference exposes .session; keep the name alive
         self.logger = logging.getLogger(__name__)
@@ -69,9 +79,19 @@ class ClusterApiClient:
         if self.api_key:                          # clusterapi_client.py:14-18
             self.headers = {"Authorization": "Bearer %s" % self.api_key, "Content-Type": "application/json"}
 
-    def _post_body(self, endpoint: str, body: bytes, name: str) -> bool:
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], **kw) -> "ClusterApiClient":
+        """Build the sink from the watcher's merged config the way the reference's (dead) factory meant to
+        (pod_watcher.py:96-108): base_url, auth.api_key, timeout, plus the retry block nobody reads upstream."""
+        c = config.get("clusterapi", {})
+        retry = c.get("retry", {})
+        return cls(c.get("base_url", "http://localhost:3000"), c.get("auth", {}).get("api_key") or None,
+                   timeout=c.get("timeout", 30), max_attempts=retry.get("max_attempts", 1),
+                   delay_seconds=retry.get("delay_seconds", 0), **kw)
+
+    def _post_once(self, endpoint: str, body: bytes, name: str) -> bool:
         try:
-            status = self.transport("POST", endpoint, body, self.headers, None)
+            status = self.transport("POST", endpoint, body, self.headers, self.timeout)
             if status == 200:
                 self.logger.info("Successfully updated pod data for %s", name)
                 return True
@@ -86,6 +106,17 @@ class ClusterApiClient:
         except Exception as e:                    # clusterapi_client.py:51-53: never raise
             self.logger.error("Unexpected error calling clusterapi: %s", e)
             return False
+
+    def _post_body(self, endpoint: str, body: bytes, name: str) -> bool:
+        """One notification, up to ``max_attempts`` tries ``delay_seconds`` apart; False only if all fail."""
+        for attempt in range(self.max_attempts):
+            if self._post_once(endpoint, body, name):
+                return True
+            if attempt + 1 < self.max_attempts:
+                self.logger.warning("Retrying %s (attempt %d of %d)", name, attempt + 2, self.max_attempts)
+                if self.delay_seconds > 0:
+                    self._sleep(self.delay_seconds)
+        return False
 
     def update_pod_status(self, pod_data: Dict[str, Any]) -> bool:
         """POST one payload to ``{base}/api/pods/update``; True iff the answer is 200

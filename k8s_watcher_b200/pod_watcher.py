@@ -317,6 +317,13 @@ class PodWatcher:
         if not self.setup_k8s_client():
             self.logger.error("Failed to setup Kubernetes client")
             return
+        # the health gate the reference has commented out (:249-253): warn and carry on
+        if self.clusterapi_client is not None:
+            if not self.clusterapi_client.health_check():
+                self.logger.warning("ClusterAPI health check failed, but continuing...")
+            else:
+                self.logger.info("ClusterAPI health check passed")
+
         self.logger.info("Starting Pod watcher in %s environment...", self.environment)
         targets = self.config.get("watcher", {}).get("namespaces", [])
         if targets:

@@ -228,3 +228,35 @@ def test_payload_fragments_rebuild_the_reference_wire_body(in_root):
         want = w._extract_pod_data(log.pod_at(i), event_timestamp="2025-01-01T00:00:00")
         want["event_type"] = log.type_at(i)
         assert body == wire_body(want)
+
+
+def test_sink_retry_timeout_and_config_factory(in_root):
+    """The knobs config/base.yaml declares (clusterapi.timeout, clusterapi.retry.*) and the reference never reads."""
+    calls, naps = [], []
+
+    def flaky(method, url, body, headers, timeout):
+        calls.append((method, timeout))
+        return 200 if len(calls) >= 3 else 503
+    w = PodWatcher("staging")
+    c = ClusterApiClient.from_config(w.config, transport=flaky, sleep=naps.append)
+    assert (c.base_url, c.timeout, c.max_attempts, c.delay_seconds) == ("http://localhost:3000", 30, 3, 2.0)
+    assert c.update_pod_status({"name": "p"}) is True            # third attempt succeeds
+    assert calls == [("POST", 30)] * 3 and naps == [2.0, 2.0]
+    calls.clear(); naps.clear()
+    always_down = ClusterApiClient("http://h", transport=MockTransport(500), max_attempts=2, delay_seconds=0)
+    assert always_down.update_pod_status({"name": "p"}) is False and len(always_down.transport.requests) == 2
+    # defaults keep the reference's behaviour: one attempt, no timeout
+    one = ClusterApiClient("http://h", transport=MockTransport(500))
+    assert one.update_pod_status({}) is False and len(one.transport.requests) == 1 and one.timeout is None
+    prod = ClusterApiClient.from_config(PodWatcher("production").config)
+    assert prod.base_url == "https://prod-clusterapi.example.com" and prod.api_key is None
+
+
+def test_health_gate_warns_and_continues(in_root, caplog):
+    import logging
+    from k8s_watcher_b200 import _k8s_stub
+    _k8s_stub.queue_events([])
+    w = PodWatcher("staging", sink=ClusterApiClient("http://h", transport=MockTransport(503)))
+    with caplog.at_level(logging.WARNING):
+        w.start_watching()                                         # empty stream: nothing to replay, no GPU needed
+    assert any("health check failed" in r.message for r in caplog.records)
