@@ -259,7 +259,7 @@ def main():
     n_surv, n_emit, n_in = float(st["n_survived"]), float(st["n_emitted"]), float(st["n_in"])
     avg = {k: v / args.steps for k, v in stage_sum.items()}
     kp = int(st["n_passes"])
-    rounds = max(1, int(st["n_launches"]) - 1 - kp - 3 - 2)      # diff_flag launches (after intern, passes, sample+init, count+scan+assemble)
+    rounds = max(1, int(st["n_diff_rounds"]))
     per_kernel = {
         # kernel: (launches per step, algorithmic bytes per launch, ms per launch)
         "intern_pack_kernel": (1, 30.0 * n_in + 8.0 * n_surv + 16.0 * n_surv, avg["ms_intern"]),

@@ -75,7 +75,7 @@ typedef struct pte_stats {
     float ms_assemble;      /* bitmap scan + compaction in replay order + payload columns */
     float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
     uint32_t n_passes;      /* radix scatter passes run */
-    uint32_t reserved;
+    uint32_t n_diff_rounds; /* diff_flag_kernel launches (position rounds) */
 } pte_stats;
 
 /* Parameters of the synthetic replay log (see "Synthetic replay logs" below). */

@@ -28,11 +28,11 @@ class PteStats(C.Structure):
         ("n_pods", C.c_uint64), ("ordered", C.c_uint32), ("n_launches", C.c_uint32),
         ("ms_total", C.c_float), ("ms_intern", C.c_float), ("ms_sort_key", C.c_float), ("ms_diff", C.c_float),
         ("ms_sort_order", C.c_float), ("ms_assemble", C.c_float), ("ms_pass_avg", C.c_float),
-        ("n_passes", C.c_uint32), ("reserved", C.c_uint32),
+        ("n_passes", C.c_uint32), ("n_diff_rounds", C.c_uint32),
     ]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+        return {n: getattr(self, n) for n, _ in self._fields_}
 
 
 class PteGenParams(C.Structure):

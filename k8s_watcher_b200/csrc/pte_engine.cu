@@ -118,7 +118,7 @@ struct pte_engine {
     Counters last{};
     // timing
     std::vector<cudaEvent_t> ev;
-    u32 n_launches = 0;
+    u32 n_launches = 0, n_diff_rounds = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pass_ev;
     size_t pass_ev_used = 0;
     // multi-GPU
@@ -540,6 +540,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     if (carry && h->carry_valid && n && h->batch_first_rv < h->stream_last_rv)
         FAIL(h, PTE_ERR_UNORDERED, "this batch starts at a resourceVersion below the end of the previous batch of the stream");
     h->n_launches = 0;
+    h->n_diff_rounds = 0;
     h->pass_ev_used = 0;
     h->has_run = false;
     cudaStream_t st = h->stream;
@@ -612,6 +613,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         const u64 bits_per_round = h->diff_round_bytes * 8;
         const u64 drounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
         const u64 span = round_up((n + drounds - 1) / drounds, 32);
+        h->n_diff_rounds = (u32)drounds;
         for (u64 r = 0; r < drounds; r++) {
             const u64 plo = r * span, phi = std::min(n, (r + 1) * span);
             if (carry) diff_flag_kernel<true><<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, plo, phi, h->state_old, h->state_new);
@@ -678,6 +680,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             sum += ms;
         }
         out->n_passes = (u32)h->pass_ev_used;
+        out->n_diff_rounds = h->n_diff_rounds;
         out->ms_pass_avg = h->pass_ev_used ? sum / h->pass_ev_used : 0.f;
     }
     return PTE_OK;
