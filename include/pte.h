@@ -48,7 +48,8 @@ enum pte_status {
     PTE_ERR_UNORDERED = -7,   /* rv decreases along arrival order and cannot be pre-sorted: span too wide
                                  (bits(rv_max - rv_min) + bits(max_events) > 64), or inside a stream batch */
     PTE_ERR_STATE = -8,       /* call out of sequence (e.g. fetch before run) */
-    PTE_ERR_NCCL = -9
+    PTE_ERR_NCCL = -9,
+    PTE_ERR_PARSE = -10       /* a line of a raw watch log could not be turned into a replay-log row */
 };
 
 enum { PTE_T_ADDED = 0, PTE_T_MODIFIED = 1, PTE_T_DELETED = 2 };
@@ -120,6 +121,22 @@ int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_
  * Stands in for the `for event in stream` producer, pod_watcher.py:264-268. */
 int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
                const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n);
+
+/* Parse a raw watch log on the device: newline-delimited JSON watch events, one per line, as the Kubernetes
+ * API streams them and the reference's loop receives them (event['type'], event['object'], pod_watcher.py:264-268):
+ *   {"type":"MODIFIED","object":{"metadata":{"uid":..,"namespace":..,"resourceVersion":..},"status":{"phase":..},..}}
+ * Keys in any order, any whitespace; the rest of the object is skipped (nesting- and string-aware).  Replaces
+ * the current log.  uid must be a 128-bit hex uid (dashes ignored); a missing resourceVersion becomes line
+ * number + 1; status absent or null -> PTE_PH_NOSTATUS, phase absent or null -> PTE_PH_NULL.  Namespaces, and phase
+ * strings other than the five well-known ones, are interned exactly on the device (ids / codes >= 7 in order of
+ * first occurrence); pte_json_strings returns the dictionaries.  On a bad line: PTE_ERR_PARSE, *bad_line = its
+ * 0-based number, and the log is left empty. */
+int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line);
+
+/* Dictionary of the last pte_ingest_json: which = 0 namespaces (index = ns_id), 1 phase strings (index = code - 7).
+ * Strings are written back to back into buf, offsets[0..n] delimit them; buf == NULL just counts (*n_out). */
+int pte_json_strings(pte_handle h, int which, char* buf, uint64_t cap, uint32_t* offsets, uint32_t max_entries,
+                     uint32_t* n_out);
 
 /* Generate the synthetic log directly in device memory (no reference counterpart). */
 int pte_generate(pte_handle h, const pte_gen_params* p);

@@ -12,7 +12,7 @@ PTE_OK = 0
 STATUS_NAMES = {
     0: "PTE_OK", -1: "PTE_ERR_INVALID", -2: "PTE_ERR_CUDA", -3: "PTE_ERR_NO_DEVICE", -4: "PTE_ERR_CAPACITY",
     -5: "PTE_ERR_TABLE_FULL", -6: "PTE_ERR_BAD_EVENT", -7: "PTE_ERR_UNORDERED", -8: "PTE_ERR_STATE",
-    -9: "PTE_ERR_NCCL",
+    -9: "PTE_ERR_NCCL", -10: "PTE_ERR_PARSE",
 }
 
 
@@ -53,6 +53,8 @@ SYMBOLS = {
     "pte_last_error": (C.c_char_p, [C.c_void_p]),
     "pte_set_filters": (C.c_int, [C.c_void_p, _u32p, C.c_int, C.c_int, C.c_int]),
     "pte_ingest": (C.c_int, [C.c_void_p, _u64p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64]),
+    "pte_ingest_json": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, _u64p, _u64p]),
+    "pte_json_strings": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_uint64, _u32p, C.c_uint32, _u32p]),
     "pte_generate": (C.c_int, [C.c_void_p, C.POINTER(PteGenParams)]),
     "pte_generate_host": (C.c_int, [C.POINTER(PteGenParams), _u64p, _u64p, _u64p, _u32p, _u8p, _u8p]),
     "pte_read_log": (C.c_int, [C.c_void_p, _u64p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, _u64p]),

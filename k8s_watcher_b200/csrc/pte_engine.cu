@@ -3,6 +3,7 @@
 // -> handle_pod_event (:214-241), plus the last-known-phase layer of SURVEY.md 8a row 7.
 #include "../../include/pte.h"
 #include "pte_kernels.cuh"
+#include "pte_json.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h>
@@ -95,6 +96,13 @@ struct pte_engine {
     u64 pay_buf_cap = 0, pay_blob_cap = 0, pay_off_cap = 0, pay_tile_cap = 0;
     u32* pay_frag_off = nullptr; u64 pay_frag_cap = 0;
     u64 *pay_rec_off = nullptr, *pay_tile_off = nullptr;
+    // raw watch-JSON ingestion
+    char* json_text = nullptr; u64 json_text_cap = 0;
+    u64* json_nl = nullptr; u64 json_nl_cap = 0;
+    u32* json_chunk_cnt = nullptr; u64 json_chunk_cap = 0;
+    u64* json_ns_keys = nullptr; u32* json_ns_off = nullptr; u64* json_ph_keys = nullptr; u32* json_ph_off = nullptr;
+    u32 *json_err = nullptr, *json_ns_remap = nullptr; u8* json_ph_remap = nullptr;
+    std::vector<std::string> json_names[2];                  // [0] namespaces by ns_id, [1] phase strings for codes >= 7
     u64* d_minmax = nullptr;
     bool in_reorder = false;
     u32 last_ordered = 1;
@@ -316,7 +324,8 @@ void pte_destroy(pte_handle h) {
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
                     h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
-                    h->pay_frag_off, h->pay_rec_off, h->pay_tile_off};
+                    h->pay_frag_off, h->pay_rec_off, h->pay_tile_off, h->json_text, h->json_nl, h->json_chunk_cnt, h->json_ns_keys, h->json_ns_off,
+                    h->json_ph_keys, h->json_ph_off, h->json_err, h->json_ns_remap, h->json_ph_remap};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
@@ -777,6 +786,133 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
     CK(h, cudaMemcpyAsync(offsets, h->pay_rec_off, count * sizeof(u64), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
     offsets[count] = total;
+    return PTE_OK;
+}
+
+static constexpr u32 kJsonNsSlots = 1u << 16, kJsonPhSlots = 128;
+
+int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line) {
+    if (!h || (!text && len)) FAIL(h, PTE_ERR_INVALID, "NULL argument");
+    if (n_events) *n_events = 0;
+    if (bad_line) *bad_line = 0;
+    if (len >= (1ull << 32) - 64) FAIL(h, PTE_ERR_CAPACITY, "watch log of 4 GiB or more: ingest it in pieces");
+    CK(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    h->has_run = false;
+    h->json_names[0].clear(); h->json_names[1].clear();
+    if (len == 0) { h->n_events = 0; return PTE_OK; }
+    int rc;
+    if ((rc = grow(h, &h->json_text, &h->json_text_cap, len + 64))) return rc;
+    CK(h, cudaMemcpyAsync(h->json_text, text, len, cudaMemcpyHostToDevice, st));
+    // 1. line index
+    const u64 chunks = (len + kJsonChunk - 1) / kJsonChunk;
+    if ((rc = grow(h, &h->json_chunk_cnt, &h->json_chunk_cap, chunks))) return rc;
+    if ((rc = grow(h, &h->pay_tile_off, &h->pay_tile_cap, chunks + 1))) return rc;
+    int grid = (int)std::min<u64>(chunks, (u64)h->num_sms * 8);
+    json_count_newlines_kernel<<<grid, 256, 0, st>>>(h->json_text, len, h->json_chunk_cnt);
+    CK(h, cudaGetLastError());
+    scan_u32_to_u64_kernel<<<1, 1024, 0, st>>>(h->json_chunk_cnt, chunks, h->pay_tile_off);
+    CK(h, cudaGetLastError());
+    u64 n_nl = 0;
+    CK(h, cudaMemcpyAsync(&n_nl, h->pay_tile_off + chunks, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    const u64 n_lines = n_nl + (text[len - 1] != '\n' ? 1 : 0);
+    if (n_lines > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "more watch events than the engine's max_events");
+    if ((rc = grow(h, &h->json_nl, &h->json_nl_cap, n_nl + 1))) return rc;
+    json_list_newlines_kernel<<<grid, 256, 0, st>>>(h->json_text, len, h->pay_tile_off, h->json_nl);
+    CK(h, cudaGetLastError());
+    // 2. dictionaries + parse
+    if (!h->json_ns_keys) {
+        CK(h, cudaMalloc((void**)&h->json_ns_keys, kJsonNsSlots * sizeof(u64)));
+        CK(h, cudaMalloc((void**)&h->json_ns_off, kJsonNsSlots * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_ph_keys, kJsonPhSlots * sizeof(u64)));
+        CK(h, cudaMalloc((void**)&h->json_ph_off, kJsonPhSlots * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_err, 2 * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_ns_remap, kJsonNsSlots * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_ph_remap, kJsonPhSlots));
+    }
+    CK(h, cudaMemsetAsync(h->json_ns_keys, 0, kJsonNsSlots * sizeof(u64), st));
+    CK(h, cudaMemsetAsync(h->json_ns_off, 0xFF, kJsonNsSlots * sizeof(u32), st));
+    CK(h, cudaMemsetAsync(h->json_ph_keys, 0, kJsonPhSlots * sizeof(u64), st));
+    CK(h, cudaMemsetAsync(h->json_ph_off, 0xFF, kJsonPhSlots * sizeof(u32), st));
+    const u32 err_init[2] = {0u, 0xFFFFFFFFu};
+    CK(h, cudaMemcpyAsync(h->json_err, err_init, sizeof(err_init), cudaMemcpyHostToDevice, st));
+    JsonArgs a;
+    a.text = h->json_text; a.len = len; a.nl = h->json_nl; a.n_lines = n_lines; a.n_nl = n_nl;
+    a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
+    a.ns_dict = StrDict{h->json_ns_keys, h->json_ns_off, kJsonNsSlots - 1};
+    a.phase_dict = StrDict{h->json_ph_keys, h->json_ph_off, kJsonPhSlots - 1};
+    a.err = h->json_err;
+    grid = (int)std::min<u64>((n_lines + 127) / 128, (u64)h->num_sms * 16);
+    json_parse_kernel<<<grid, 128, 0, st>>>(a);
+    CK(h, cudaGetLastError());
+    u32 err[2];
+    CK(h, cudaMemcpyAsync(err, h->json_err, sizeof(err), cudaMemcpyDeviceToHost, st));
+    std::vector<u64> nk(kJsonNsSlots), pk(kJsonPhSlots);
+    std::vector<u32> no(kJsonNsSlots), po(kJsonPhSlots);
+    CK(h, cudaMemcpyAsync(nk.data(), h->json_ns_keys, nk.size() * 8, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(no.data(), h->json_ns_off, no.size() * 4, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(pk.data(), h->json_ph_keys, pk.size() * 8, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(po.data(), h->json_ph_off, po.size() * 4, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    if (err[0]) {
+        static const char* why[] = {"", "malformed JSON", "event type is not ADDED/MODIFIED/DELETED", "metadata.uid is not a 128-bit hex uid",
+                                    "metadata.resourceVersion is not a decimal number", "a field the path reads contains an escape sequence",
+                                    "more distinct namespaces than the device dictionary holds", "too many distinct phase strings"};
+        if (bad_line) *bad_line = err[1];
+        h->n_events = 0;
+        FAIL(h, PTE_ERR_PARSE, std::string("watch log line ") + std::to_string(err[1]) + ": " + why[std::min<u32>(err[0], 7)]);
+    }
+    // 3. dictionary slots -> dense ids in order of first occurrence (deterministic), names kept for the host
+    auto build = [&](const std::vector<u64>& keys, const std::vector<u32>& offs, std::vector<std::string>& names, std::vector<u32>& remap) {
+        std::vector<std::pair<u32, u32>> occ;      // (first offset, slot)
+        for (u32 sl = 0; sl < keys.size(); sl++) if (keys[sl]) occ.emplace_back(offs[sl], sl);
+        std::sort(occ.begin(), occ.end());
+        remap.assign(keys.size(), 0);
+        for (u32 id = 0; id < occ.size(); id++) {
+            const u32 sl = occ[id].second, l = (u32)(keys[sl] & 0xFFFFFu);
+            names.emplace_back(text + occ[id].first, l);
+            remap[sl] = id;
+        }
+    };
+    std::vector<u32> nremap, premap32;
+    build(nk, no, h->json_names[0], nremap);
+    build(pk, po, h->json_names[1], premap32);
+    if (h->json_names[1].size() > kPhMax - 6) {
+        h->n_events = 0;
+        FAIL(h, PTE_ERR_PARSE, "more than 56 distinct phase strings besides the five well-known ones");
+    }
+    std::vector<u8> premap(kJsonPhSlots, 0);
+    for (u32 sl = 0; sl < kJsonPhSlots; sl++) premap[sl] = (u8)(7 + premap32[sl]);
+    CK(h, cudaMemcpyAsync(h->json_ns_remap, nremap.data(), nremap.size() * 4, cudaMemcpyHostToDevice, st));
+    CK(h, cudaMemcpyAsync(h->json_ph_remap, premap.data(), premap.size(), cudaMemcpyHostToDevice, st));
+    grid = (int)std::min<u64>((n_lines + 255) / 256, (u64)h->num_sms * 16);
+    json_remap_kernel<<<grid, 256, 0, st>>>(h->ns, h->phase, n_lines, h->json_ns_remap, h->json_ph_remap);
+    CK(h, cudaGetLastError());
+    u64 ends[2] = {0, 0};
+    CK(h, cudaMemcpyAsync(&ends[0], h->rv, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(&ends[1], h->rv + n_lines - 1, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    h->n_events = n_lines;
+    h->batch_first_rv = ends[0]; h->batch_last_rv = ends[1];
+    if (n_events) *n_events = n_lines;
+    return PTE_OK;
+}
+
+int pte_json_strings(pte_handle h, int which, char* buf, uint64_t cap, uint32_t* offsets, uint32_t max_entries, uint32_t* n_out) {
+    if (!h || !n_out || which < 0 || which > 1) FAIL(h, PTE_ERR_INVALID, "bad argument");
+    const auto& v = h->json_names[which];
+    *n_out = (u32)v.size();
+    if (!buf || !offsets) return PTE_OK;
+    if (v.size() > max_entries) FAIL(h, PTE_ERR_CAPACITY, "offset array too small");
+    u64 o = 0;
+    for (size_t i = 0; i < v.size(); i++) {
+        if (o + v[i].size() > cap) FAIL(h, PTE_ERR_CAPACITY, "string buffer too small");
+        offsets[i] = (u32)o;
+        memcpy(buf + o, v[i].data(), v[i].size());
+        o += v[i].size();
+    }
+    offsets[v.size()] = (u32)o;
     return PTE_OK;
 }
 

@@ -158,6 +158,25 @@ class PhaseTransitionEngine:
                                     _ptr(c["rv"], C.c_uint64), _ptr(c["ns_id"], C.c_uint32),
                                     _ptr(c["phase"], C.c_uint8), _ptr(c["type"], C.c_uint8), n))
 
+    def ingest_json(self, text: bytes) -> int:
+        """Parse a raw watch log (newline-delimited JSON watch events) on the device into the log columns.
+        Returns the number of events; raises PteError(PTE_ERR_PARSE) naming the first bad line."""
+        n, bad = C.c_uint64(), C.c_uint64()
+        self._ck(self._L.pte_ingest_json(self._h, text, len(text), C.byref(n), C.byref(bad)))
+        return int(n.value)
+
+    def json_strings(self, which: int) -> list:
+        """Dictionary of the last ingest_json: 0 = namespaces by ns_id, 1 = phase strings for codes 7, 8, ..."""
+        n = C.c_uint32()
+        self._ck(self._L.pte_json_strings(self._h, which, None, 0, None, 0, C.byref(n)))
+        if n.value == 0:
+            return []
+        buf = C.create_string_buffer(1 << 20)
+        off = np.zeros(n.value + 1, np.uint32)
+        self._ck(self._L.pte_json_strings(self._h, which, buf, len(buf), _ptr(off, C.c_uint32), n.value, C.byref(n)))
+        raw = buf.raw
+        return [raw[int(off[i]):int(off[i + 1])].decode("utf-8") for i in range(n.value)]
+
     def generate(self, seed: int, n_events: int, n_pods: int, **kw):
         p = gen_params(seed, n_events, n_pods, **kw)
         self._ck(self._L.pte_generate(self._h, C.byref(p)))

@@ -298,6 +298,20 @@ class PodWatcher:
         self.batches.append(batch)
         return batch
 
+    def replay_watch_json(self, text: bytes, *, dedupe: Optional[bool] = None, max_events: int = 0, max_pods: int = 0) -> Batch:
+        """Replay a raw watch log (newline-delimited JSON watch events, what ``for event in stream`` would have
+        yielded, :264-268): parsed, interned and replayed on the device."""
+        dedupe = self.dedupe if dedupe is None else dedupe
+        n_lines = text.count(b"\n") + 1
+        eng = self._engine_for(max(max_events, n_lines), max_pods)
+        log = ReplayLog.from_watch_json(eng, text)
+        names = self.config.get("watcher", {}).get("namespaces", []) or []
+        eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
+        stats = eng.run(dedupe=dedupe)
+        batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
+        self.batches.append(batch)
+        return batch
+
     def flush(self) -> Optional[Batch]:
         """Replay everything queued by handle_pod_event; hand the result to the sink if there is one."""
         if not self._pending:

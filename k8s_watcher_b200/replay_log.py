@@ -78,6 +78,14 @@ class ReplayLog:
         return cls(cols, names, phases, pods)
 
     @classmethod
+    def from_watch_json(cls, engine, text: bytes) -> "ReplayLog":
+        """Raw watch log (newline-delimited JSON watch events) -> replay log, parsed and interned on the device
+        (pte_ingest_json).  The log is left resident in ``engine``, ready for ``engine.run()``."""
+        engine.ingest_json(text)
+        phases = list(codes.PHASE_NAMES) + [None, None] + engine.json_strings(1)
+        return cls(engine.read_log(), engine.json_strings(0), phases)
+
+    @classmethod
     def synthetic(cls, seed: int, n_events: int, n_pods: int, **kw) -> "ReplayLog":
         """The synthetic log of include/pte.h (host generator of libpte.so)."""
         return cls(generate_host(seed, n_events, n_pods, **kw), list(codes.DEFAULT_NAMESPACES))

@@ -174,3 +174,48 @@ def events_from_columns(cols, *, rich: bool = True):
                        rich=rich, resource_version=int(cols["rv"][i]))
         out.append({"type": TYPE_STR[int(cols["type"][i])], "object": pod})
     return out
+
+
+def watch_json_lines(events, *, seed: int = 0, compact: bool = True) -> bytes:
+    """The watch stream as the Kubernetes API would send it: one JSON watch event per line
+    (``{"type": ..., "object": {...pod...}}``, API field names), keys in a per-line shuffled order, plus
+    look-alike keys deeper down (ownerReferences[].uid, an annotation whose text contains ``"phase"``) that a
+    parser must not confuse with the fields the watcher reads (pod_watcher.py:162-167, :216-217)."""
+    import json
+    import random
+    rnd = random.Random(seed)
+
+    def shuffled(d):
+        items = list(d.items())
+        rnd.shuffle(items)
+        return dict(items)
+
+    lines = []
+    for ev in events:
+        pod = ev["object"]
+        md = pod.metadata
+        meta = {"name": md.name, "namespace": md.namespace, "uid": md.uid,
+                "ownerReferences": [{"kind": "ReplicaSet", "uid": "00000000-dead-beef-0000-000000000000", "name": "rs"}],
+                "annotations": dict(md.annotations or {}, note='fake {"phase":"Failed","uid":"x"} \\ "quoted"'),
+                "labels": md.labels or {}}
+        if md.resource_version is not None:
+            meta["resourceVersion"] = md.resource_version
+        if md.creation_timestamp is not None:
+            meta["creationTimestamp"] = md.creation_timestamp.isoformat() + "Z"
+        obj = {"kind": "Pod", "apiVersion": "v1", "metadata": shuffled(meta)}
+        if pod.spec is not None:
+            obj["spec"] = {"nodeName": pod.spec.node_name,
+                           "containers": [{"name": c.name, "image": c.image, "env": [{"name": "phase", "value": "Running"}]}
+                                          for c in (pod.spec.containers or [])]}
+        if pod.status is not None:
+            st = {"conditions": [{"type": c.type, "status": c.status, "phase": "decoy"} for c in (pod.status.conditions or [])],
+                  "hostIP": "10.0.0.1"}
+            if pod.status.phase is not None or rnd.random() < 0.5:
+                st["phase"] = pod.status.phase            # None -> JSON null; sometimes the key is simply absent
+            obj["status"] = shuffled(st)
+        elif rnd.random() < 0.5:
+            obj["status"] = None                           # "status": null is as falsy as a missing status
+        line = json.dumps(shuffled({"type": ev["type"], "object": shuffled(obj)}),
+                          separators=(",", ":") if (compact and rnd.random() < 0.7) else None)
+        lines.append(line)
+    return ("\n".join(lines) + ("\n" if rnd.random() < 0.5 or not lines else "")).encode()

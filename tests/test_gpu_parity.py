@@ -448,3 +448,58 @@ def test_device_wire_bodies_match_requests_bytes(monkeypatch):
     assert [raw[int(off[i]):int(off[i + 1])] for i in range(1100)] == want[1500:2600]
     empty = w.replay(ReplayLog.synthetic(1, 0, 1))
     assert empty.wire_bodies(event_timestamp=ts) == []
+
+
+# ---- raw watch-JSON ingestion on the device ----------------------------------------
+def _json_case(n, pods, seed, **gen):
+    cols = c_oracle.generate(seed, n, pods, **gen)
+    events = fk.events_from_columns(cols)
+    # a few pods in phases outside the well-known five, and one in a namespace that needs no escaping but is new
+    for k in range(0, n, 97):
+        if events[k]["object"].status is not None:
+            events[k]["object"].status.phase = ("Terminating", "Evicted", "ContainerCreating")[k % 3]
+    return events, fk.watch_json_lines(events, seed=seed)
+
+
+@pytest.mark.parametrize("n,pods,seed", [(1, 1, 1), (2_000, 60, 2), (60_000, 900, 3)])
+def test_watch_json_parses_to_the_same_columns_as_the_host_interner(n, pods, seed):
+    events, text = _json_case(n, pods, seed, dist=1, p_del=0.08, p_nostatus=0.05, p_null=0.05)
+    want = ReplayLog.from_events(events)
+    with PhaseTransitionEngine(max(n, 1024), pods) as e:
+        got = ReplayLog.from_watch_json(e, text)
+    assert len(got) == n
+    for k in ("uid_hi", "uid_lo", "rv", "type"):
+        assert np.array_equal(got.columns[k], want.columns[k]), k
+    # ids are handed out in order of first occurrence on both sides, so even the codes agree
+    assert got.namespaces == want.namespaces and np.array_equal(got.columns["ns_id"], want.columns["ns_id"])
+    assert got.phases == want.phases and np.array_equal(got.columns["phase"], want.columns["phase"])
+
+
+@pytest.mark.parametrize("env", ["development", "staging", "production"])
+def test_replay_of_watch_json_matches_reference_semantics(env, monkeypatch):
+    monkeypatch.chdir(ROOT)
+    events, text = _json_case(20_000, 300, 11, dist=0, p_del=0.1, p_nostatus=0.05, p_null=0.05)
+    w = PodWatcher(env)
+    batch = w.replay_watch_json(text)
+    # oracle: the reference's filters on the very same pod objects, then the transition layer
+    r = po.reference_trace(env, w.config, [(e["type"], e["object"]) for e in events], "T")
+    keep = po.transition_filter(r)
+    reach = [i for i, e in enumerate(events) if po.reaches_post_site(env, w.config, e["type"], e["object"])]
+    assert batch.indices.tolist() == [reach[k] for k in keep]
+
+
+@pytest.mark.parametrize("bad,reason", [
+    (b'{"type":"ADDED","object":{"metadata":{"uid":"zz","namespace":"a"}}}', "uid"),
+    (b'{"type":"BOOKMARK","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001"}}}', "type"),
+    (b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001","resourceVersion":"12x"}}}', "resourceVersion"),
+    (b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001"}', "malformed"),
+    (b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001","namespace":"a\\\\u0062"}}}', "escape"),
+])
+def test_watch_json_bad_lines_are_named(bad, reason):
+    good = b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-00000000000a","namespace":"x","resourceVersion":"5"},"status":{"phase":"Running"}}}'
+    with PhaseTransitionEngine(1024, 16) as e:
+        with pytest.raises(PteError) as ei:
+            e.ingest_json(good + b"\n" + good + b"\n" + bad + b"\n" + good + b"\n")
+        assert ei.value.code == -10 and "line 2" in str(ei.value) and reason in str(ei.value)
+        assert e.ingest_json(good + b"\n" + good) == 2          # and the engine is still usable
+        assert e.json_strings(0) == ["x"]
