@@ -294,12 +294,20 @@ def main():
     # ---- end to end through host buffers (rank-local; max over ranks)
     e2e = None
     if not args.no_e2e:
-        e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier)
+        import psutil
+        budget = 0.5 * psutil.virtual_memory().available / world          # all ranks share one host
+        m = ev if 35.0 * ev <= budget else max(1 << 20, int(budget / 35.0) // (1 << 20) * (1 << 20))
+        if world > 1:                                                      # every rank uses the same size
+            m = int(sharding.gather_counts_pg(dist_t, [m, 0, 0, 0])[:, 0].min())
+        e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m)
         if world > 1:
             e2e["ms_per_step"] = sharding.max_over_ranks(dist_t, [e2e["ms_per_step"]])[0]
             b = sharding.gather_counts_pg(dist_t, [e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"], 0, 0])
             e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"] = int(b[:, 0].sum()), int(b[:, 1].sum())
-        e2e["value"] = sharding.throughput(total_events, e2e["ms_per_step"])
+        e2e_events = e2e["events_per_gpu"]
+        if world > 1:
+            e2e_events = int(sharding.gather_counts_pg(dist_t, [e2e_events, 0, 0, 0])[:, 0].sum())
+        e2e["value"] = sharding.throughput(e2e_events, e2e["ms_per_step"])
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -346,15 +354,20 @@ def _traffic():
         return {}
 
 
-def _e2e(eng, args, np, PinnedBuffer, ev, barrier):
+def _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m):
     """What PodWatcher.replay does per batch: pte_ingest (pinned host columns -> HBM) + pte_run + pte_fetch of the
-    arrival index and event type of every notification (the host still holds the log, so that is the result)."""
+    arrival index and event type of every notification (the host still holds the log, so that is the result).
+    All ranks share one host: if 35 B/event x events x ranks does not fit in half of the free host memory, every
+    rank runs this leg on a prefix-sized log of the same shape (same events-per-pod ratio) and says so."""
+    if m < ev:
+        _, pods, dist, p_del, _ = wl
+        eng.generate(SEED, m, max(1, int(pods * (m / ev))), dist=dist, p_del=p_del, shard=rank, n_shards=world)
     dts = (("uid_hi", np.uint64), ("uid_lo", np.uint64), ("rv", np.uint64), ("ns_id", np.uint32), ("phase", np.uint8),
            ("type", np.uint8))
-    pins = {k: PinnedBuffer(ev, dt) for k, dt in dts}
+    pins = {k: PinnedBuffer(m, dt) for k, dt in dts}
     host = eng.read_log(into={k: p.array for k, p in pins.items()})           # set-up, untimed
     odts = dict(idx=np.uint32, type=np.uint8)
-    opins = {k: PinnedBuffer(ev, dt) for k, dt in odts.items()}
+    opins = {k: PinnedBuffer(m, dt) for k, dt in odts.items()}
     out = {k: p.array for k, p in opins.items()}
     eng.ingest(host); eng.run(); eng.fetch(columns=(), into=out)              # warm-up
     barrier()
@@ -365,9 +378,11 @@ def _e2e(eng, args, np, PinnedBuffer, ev, barrier):
         got = eng.fetch(columns=(), into=out)
     ms = (time.perf_counter() - t0) * 1e3 / args.e2e_steps
     barrier()
-    res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps,
-           "h2d_bytes_per_step": 30 * ev, "d2h_bytes_per_step": 5 * len(got),
+    res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps, "events_per_gpu": m,
+           "h2d_bytes_per_step": 30 * m, "d2h_bytes_per_step": 5 * len(got),
            "api": "pte_ingest + pte_run + pte_fetch(idx, type) with pinned host buffers (= PodWatcher.replay)"}
+    if m < ev:
+        res["reduced"] = "host memory: %d ranks x 35 B x %d events do not fit in half of the free RAM; same shape, %d events per GPU" % (world, ev, m)
     for p in list(pins.values()) + list(opins.values()):
         p.free()
     return res
