@@ -1,9 +1,16 @@
-// Device kernels of the replay path other than the sort:
-//   intern_pack_kernel   filters (pod_watcher.py:204-212, :226-229) + uid interning + record packing
-//   diff_flag_kernel     segmented adjacent-diff on the key-sorted records -> emit bitmap
-//   assemble_*_kernel    scan/compaction of the bitmap in replay order -> payload columns (pod_watcher.py:232-236)
-//   digest_kernel        order-sensitive digest for large-scale parity
-//   gen_* kernels        synthetic replay logs (spec in include/pte.h)
+// Device kernels of the replay path other than the sort (pte_radix.cuh) and the JSON scanner (pte_json.cuh):
+//   filter_flag_kernel    the reference's two predicates (pod_watcher.py:204-212, :226-229) + rv order check -> keep bitmap
+//   intern_pack_kernel    uid interning (exact, 128-bit CAS dictionary) + record packing + digit histograms
+//   diff_sample/bitmap_init/diff_flag kernels
+//                         segmented adjacent-diff on the key-sorted records -> emit bitmap,
+//                         optionally against the per-pod state carried from earlier batches of a stream
+//   bitmap_count/tile_scan/assemble_bitmap kernels
+//                         scan + compaction of the bitmap in replay order -> payload columns (pod_watcher.py:232-236)
+//   key_lookup_kernel     interned key of every emitted record, on demand
+//   payload_* kernels     request bodies as `requests` would send them (clusterapi_client.py:36)
+//   rv_* / permute_log / map_idx kernels   pre-sort of logs that are not in resourceVersion order
+//   digest_kernel         order-sensitive digest for large-scale parity
+//   gen_* kernels         synthetic replay logs (spec in include/pte.h)
 #pragma once
 #include "pte_common.cuh"
 #include "pte_radix.cuh"
