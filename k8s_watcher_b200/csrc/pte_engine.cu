@@ -589,7 +589,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             intern_pack_kernel<true><<<grid, kInternThreads, 0, st>>>(a);
             h->n_launches += 3;
         } else {
-            int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
+            int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * PTE_INTERN_BLOCKS);
             intern_pack_kernel<false><<<grid, kInternThreads, 0, st>>>(a);
         }
         CK(h, cudaGetLastError());
@@ -649,7 +649,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         CK(h, cudaGetLastError());
         tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, n, h->ctr);
         CK(h, cudaGetLastError());
-        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 6);
+        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * PTE_ASM_BLOCKS);
         assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
         CK(h, cudaGetLastError());
         h->n_launches += 3;

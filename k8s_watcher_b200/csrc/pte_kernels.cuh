@@ -108,6 +108,10 @@ struct InternArgs {
 };
 
 static constexpr int kAsmTile = 256 * 32;       // positions per bitmap tile (256 words)
+#ifndef PTE_ASM_ROWS
+#define PTE_ASM_ROWS 4
+#endif
+static constexpr int kAsmRows = PTE_ASM_ROWS;   // rows a thread of assemble_bitmap_kernel keeps in flight
 static constexpr int kInternThreads = 256;
 static constexpr int kInternPerThread = 4;
 static constexpr int kInternTile = kInternThreads * kInternPerThread;
@@ -133,8 +137,11 @@ __device__ __forceinline__ bool passes_filters(const InternArgs& a, u32 ty, u32 
 //                    ticket and no look-back: the blocks are independent.
 // (Interning in several rounds over L2-sized slices of the dictionary was tried and is slower: probes
 //  that hit L2 only halve the kernel, and every round has to re-read the uid columns.)
+#ifndef PTE_INTERN_BLOCKS
+#define PTE_INTERN_BLOCKS 5      // measured on B200: 3/4/5/6 CTAs per SM -> 29.1/24.7/23.7/28.3 ms (6 spills too much)
+#endif
 template <bool FILTERED>
-__global__ void __launch_bounds__(kInternThreads) intern_pack_kernel(InternArgs a) {
+__global__ void __launch_bounds__(kInternThreads, FILTERED ? 4 : PTE_INTERN_BLOCKS) intern_pack_kernel(InternArgs a) {
     __shared__ u32 s_tot[8];
     __shared__ u32 s_hist[4 * kRadix];     // the sort's digit counts are taken here: no extra read of the records
     const u32 tid = threadIdx.x, lane = tid & 31;
@@ -484,7 +491,10 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(u32* __restrict__ tile_
     for (u32 t = lo; t < hi; t++) { u32 v = tile_count[t]; tile_count[t] = run; run += v; }
 }
 
-__global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a) {
+#ifndef PTE_ASM_BLOCKS
+#define PTE_ASM_BLOCKS 4         // measured: (rows, CTAs/SM) (4,6) 7.5 ms with spills, (4,4) 5.9 ms, (8,3) 5.8 ms
+#endif
+__global__ void __launch_bounds__(256, PTE_ASM_BLOCKS) assemble_bitmap_kernel(AssembleArgs a) {
     __shared__ unsigned short s_pos[kAsmTile];
     __shared__ u32 s_tot[8];
     const u32 tid = threadIdx.x;
@@ -503,13 +513,13 @@ __global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a)
         }
         __syncthreads();
         const u64 tbase = (u64)tile * kAsmTile, obase = a.lookback[tile];      // tile offsets from tile_scan_kernel
-        // four rows per thread and iteration, all gathers issued before the first store
-        for (u32 j0 = tid; j0 < cnt; j0 += 4 * 256) {
-            u32 idx[4], ns[4];
-            u64 rv[4];
-            u8 ph[4], ty[4];
+        // kAsmRows rows per thread and iteration, all gathers issued before the first store
+        for (u32 j0 = tid; j0 < cnt; j0 += kAsmRows * 256) {
+            u32 idx[kAsmRows], ns[kAsmRows];
+            u64 rv[kAsmRows];
+            u8 ph[kAsmRows], ty[kAsmRows];
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
+            for (int k = 0; k < kAsmRows; k++) {
                 const u32 j = j0 + k * 256;
                 if (j < cnt) {
                     idx[k] = (u32)(tbase + s_pos[j]);
@@ -520,11 +530,11 @@ __global__ void __launch_bounds__(256, 6) assemble_bitmap_kernel(AssembleArgs a)
                 }
             }
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
+            for (int k = 0; k < kAsmRows; k++) {
                 const u32 j = j0 + k * 256;
                 if (j < cnt) {
                     const u64 o = obase + j;
-                    a.out_idx[o] = idx[k]; a.out_rv[o] = rv[k]; a.out_ns[o] = ns[k];
+                    __stcs(a.out_idx + o, idx[k]); __stcs(a.out_rv + o, rv[k]); __stcs(a.out_ns + o, ns[k]);
                     a.out_phase[o] = ph[k]; a.out_type[o] = ty[k];
                 }
             }
