@@ -109,8 +109,9 @@ struct RadixPassSmem {
 //   eight ballots    ~22 cycles of the vote path plus ~40 ALU-pipe instructions;
 //   shared atomicOr  every lane ORs its lane bit into the warp's mask word of its digit and reads the
 //                    word back: under 3 cycles per op, but ~3.4 bank-conflict wavefronts each.
-// The pass mixes the last two (BALLOT_ITEMS of a thread's records use ballots, the rest atomics) so
-// that neither the ALU pipe nor the shared-memory pipe is the only one busy.
+// The pass uses the atomicOr form.  BALLOT_ITEMS > 0 ranks that many of a thread's records with ballots
+// instead (the two forms load different pipes), kept as a tuning option: every mix measured slower than
+// all-atomic on B200 (profiles/README.md).
 template <bool CHECK_VALID>
 __device__ __forceinline__ u32 rank_by_ballot(u32* __restrict__ warp_off, u32 d, bool valid, u32 lt) {
     u32 peers = 0xffffffffu;
