@@ -52,8 +52,15 @@ __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo,
 
 static constexpr int kMaxProbe = 2048;
 
-// Dictionary slots are read with an L2 evict_last hint: the log streams through L2 with evict_first
-// (ld/st .cs), so the 126 MB L2 ends up holding mostly dictionary lines without any carve-out.
+// Dictionary slots are read with an L2 evict_last hint, the log streams through with evict_first (ld/st .cs).
+// Measured (profiles/README.md, r01_gather/): the hint changes nothing -- a random probe over a table of twice
+// the L2 hits 26 % of the time with or without it, a miss always brings in the whole 128-byte line, and the
+// kernel is bound by the rate of random lines (46 G/s of the 54 G/s a bare gather reaches), not by bytes.
+// PTE_SLOT_LD picks the load for tuning builds: 0 evict_last hint (default), 1 L2::64B (half the DRAM bytes per
+// miss, but 26.0 instead of 23.7 ms: the next slot of a probe run misses more often), 2 both, 3 plain.
+#ifndef PTE_SLOT_LD
+#define PTE_SLOT_LD 0
+#endif
 __device__ __forceinline__ u64 l2_policy_evict_last() {
     u64 pol;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
@@ -61,7 +68,15 @@ __device__ __forceinline__ u64 l2_policy_evict_last() {
 }
 __device__ __forceinline__ ulonglong2 ld_slot(const Slot* p, u64 pol) {
     ulonglong2 v;
+#if PTE_SLOT_LD == 1
+    asm volatile("ld.global.L2::64B.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+#elif PTE_SLOT_LD == 2
+    asm volatile("ld.global.L2::cache_hint.L2::64B.v2.u64 {%0, %1}, [%2], %3;" : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(pol) : "memory");
+#elif PTE_SLOT_LD == 3
+    asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+#else
     asm volatile("ld.global.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;" : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(pol) : "memory");
+#endif
     return v;
 }
 

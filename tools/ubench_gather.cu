@@ -1,0 +1,118 @@
+// What does one random 16-byte dictionary probe cost on B200?  Random aligned loads over a table of a
+// given size, four independent loads in flight per thread (the shape of intern_pack_kernel's probes).
+// Prints useful GB/s and loads/s; run under `ncu --metrics dram__bytes_read.sum,lts__t_sectors_op_read.sum`
+// to get DRAM bytes per load.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench_gather tools/ubench_gather.cu
+// Run  : tools/ubench_gather <table MB> [fetch-granularity limit]
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+__device__ __forceinline__ u64 mix64(u64 z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+enum { PLAIN16, CG16, NC16, EVICT_FIRST16, EVICT_LAST16, NOALLOC16, PF64_16, PF128_16, PLAIN8, PAIR32, CV16, N_MODES };
+const char* kNames[N_MODES] = {"ld.global.v2.u64", "ld.global.cg.v2.u64", "ld.global.nc.v2.u64", "cache_hint evict_first", "cache_hint evict_last",
+                               "L1::no_allocate", "ld.global.L2::64B", "ld.global.L2::128B", "ld.global.u64 (8 B)", "2 x 16 B in one sector", "ld.volatile (cv)"};
+
+template <int MODE>
+__device__ __forceinline__ u64 probe(const ulonglong2* t, u64 slot, u64 pol) {
+    const ulonglong2* p = t + slot;
+    ulonglong2 v = make_ulonglong2(0, 0);
+    if (MODE == PLAIN16) asm volatile("ld.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == CG16) asm volatile("ld.global.cg.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == CV16) asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == NC16) asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == EVICT_FIRST16 || MODE == EVICT_LAST16)
+        asm volatile("ld.global.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;" : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(pol));
+    if (MODE == NOALLOC16) asm volatile("ld.global.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == PF64_16) asm volatile("ld.global.L2::64B.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == PF128_16) asm volatile("ld.global.L2::128B.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == PLAIN8) asm volatile("ld.global.u64 %0, [%1];" : "=l"(v.x) : "l"(p));
+    if (MODE == PAIR32) {
+        const ulonglong2* q = t + (slot & ~1ull);
+        ulonglong2 w;
+        asm volatile("ld.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(q));
+        asm volatile("ld.global.v2.u64 {%0,%1}, [%2];" : "=l"(w.x), "=l"(w.y) : "l"(q + 1));
+        v.x ^= w.x; v.y ^= w.y;
+    }
+    return v.x ^ v.y;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) gather(const ulonglong2* __restrict__ t, u64 mask, u64 per_thread, u64 seed, u64* out) {
+    u64 pol = 0;
+    if (MODE == EVICT_FIRST16) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    if (MODE == EVICT_LAST16) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    u64 acc = 0;
+    for (u64 i = 0; i < per_thread; i += 4) {
+        u64 s[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) s[k] = mix64(seed + (gid * per_thread + i + k) * 0x9E3779B97F4A7C15ull) & mask;
+        u64 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = probe<MODE>(t, s[k], pol);
+        acc += v[0] ^ v[1] ^ v[2] ^ v[3];
+    }
+    if (acc == 0x1234567ull) out[0] = acc;      // keeps the loads alive
+}
+
+template <int MODE>
+void run(const ulonglong2* t, u64 slots, u64* out) {
+    const int blocks = 148 * 8;
+    const u64 per_thread = 1024;
+    const u64 loads = (u64)blocks * 256 * per_thread;
+    gather<MODE><<<blocks, 256>>>(t, slots - 1, per_thread, 1, out);
+    cudaDeviceSynchronize();
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    gather<MODE><<<blocks, 256>>>(t, slots - 1, per_thread, 2, out);
+    cudaEventRecord(b);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    const double bytes = MODE == PLAIN8 ? 8 : (MODE == PAIR32 ? 32 : 16);
+    printf("  %-26s %8.3f ms  %7.2f G loads/s  %7.1f GB/s useful\n", kNames[MODE], ms, loads / ms * 1e-6, loads * bytes / ms * 1e-6);
+}
+
+int main(int argc, char** argv) {
+    const u64 mb = argc > 1 ? strtoull(argv[1], nullptr, 10) : 256;
+    if (argc > 2) {
+        cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(argv[2]));
+        size_t got = 0;
+        cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+        printf("fetch-granularity limit: asked %s, set -> %s, now %zu\n", argv[2], cudaGetErrorString(e), got);
+    } else {
+        size_t got = 0;
+        cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+        printf("fetch-granularity limit (default): %zu\n", got);
+    }
+    u64 slots = 1;
+    while (slots * 16 < mb << 20) slots <<= 1;
+    ulonglong2* t;
+    u64* out;
+    if (cudaMalloc(&t, slots * 16) != cudaSuccess || cudaMalloc(&out, 8) != cudaSuccess) { printf("alloc failed\n"); return 1; }
+    cudaMemset(t, 1, slots * 16);
+    printf("table %llu MB (%llu slots of 16 B), %d x 256 threads, 4 loads in flight per thread\n", slots * 16 >> 20, slots, 148 * 8);
+    run<PLAIN16>(t, slots, out);
+    run<CG16>(t, slots, out);
+    run<CV16>(t, slots, out);
+    run<NC16>(t, slots, out);
+    run<NOALLOC16>(t, slots, out);
+    run<EVICT_FIRST16>(t, slots, out);
+    run<EVICT_LAST16>(t, slots, out);
+    run<PF64_16>(t, slots, out);
+    run<PF128_16>(t, slots, out);
+    run<PLAIN8>(t, slots, out);
+    run<PAIR32>(t, slots, out);
+    cudaError_t e = cudaDeviceSynchronize();
+    printf("%s\n", cudaGetErrorString(e));
+    return e == cudaSuccess ? 0 : 1;
+}
