@@ -113,6 +113,7 @@ struct pte_engine {
     u64 diff_round_bytes = 64ull << 20;      // bitmap bytes one diff round may touch
     bool key_valid = false;                  // out_key holds the keys of the last run
     bool no_invert = false;                  // PTE_NO_INVERT=1: always set emitted bits (tuning / tests)
+    bool no_defer = false;                   // PTE_NO_DEFER=1: one diff launch (and one read of the records) per bitmap slice
     Counters* ctr = nullptr;
     // filters
     u32* ns_bitmap = nullptr;
@@ -358,6 +359,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
         return PTE_ERR_CAPACITY;
     }
     if (const char* ni = getenv("PTE_NO_INVERT")) h->no_invert = atoi(ni) != 0;
+    if (const char* nd = getenv("PTE_NO_DEFER")) h->no_defer = atoi(nd) != 0;
     if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
     const char* cfg = getenv("PTE_PASS_CFG");
     if (cfg) h->pass_cfg = std::min(std::max(atoi(cfg), 0), kNumPassCfgs - 1);
@@ -583,8 +585,6 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             CK(h, cudaGetLastError());
             tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, n, h->ctr);
             CK(h, cudaGetLastError());
-            // filter_flag counted the DELETED survivors as tombstones (right for the R-trace); the diff stage recounts
-            CK(h, cudaMemsetAsync(&h->ctr->n_tombstones, 0, sizeof(u64), st));
             int grid = (int)std::min<u64>(blocks, (u64)h->num_sms * 8);
             intern_pack_kernel<true><<<grid, kInternThreads, 0, st>>>(a);
             h->n_launches += 3;
@@ -608,7 +608,8 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
                             h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev[2], st));
-        int grid = (int)std::min<u64>((n + 511) / 512, (u64)h->num_sms * 16);
+        const u64 per_cta = (u64)kDiffThreads * kDiffPerThread;
+        int grid = (int)std::min<u64>((n + per_cta - 1) / per_cta, (u64)h->num_sms * 16);
         // polarity: flip the bits of the minority (emitted or suppressed), estimated from a sample.  Stream
         // batches keep the plain polarity (their segment heads depend on the carried state, not on the record).
         const u64 sample = 4u << 20;
@@ -618,17 +619,40 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             h->bitmap, filtered ? h->keepmap : nullptr, n, h->ctr, (carry || h->no_invert) ? 0 : 1);
         CK(h, cudaGetLastError());
         h->n_launches += 2;
-        // rounds: each touches a slice of the bitmap small enough to stay in L2
+        // slices: each covers a part of the bitmap small enough to stay in L2 while it is being flipped
         const u64 bits_per_round = h->diff_round_bytes * 8;
         const u64 drounds = std::max<u64>(1, (n + bits_per_round - 1) / bits_per_round);
         const u64 span = round_up((n + drounds - 1) / drounds, 32);
-        h->n_diff_rounds = (u32)drounds;
-        for (u64 r = 0; r < drounds; r++) {
-            const u64 plo = r * span, phi = std::min(n, (r + 1) * span);
-            if (carry) diff_flag_kernel<true><<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, plo, phi, h->state_old, h->state_new);
-            else diff_flag_kernel<false><<<grid, 256, 0, st>>>(sorted, n_surv_ptr, h->bitmap, h->L, h->ctr, plo, phi, nullptr, nullptr);
+        DiffArgs d;
+        d.in = sorted; d.n_ptr = n_surv_ptr; d.bitmap = h->bitmap; d.L = h->L; d.ctr = h->ctr;
+        d.state_old = carry ? h->state_old : nullptr; d.state_new = carry ? h->state_new : nullptr;
+        d.defer_list = nullptr; d.defer_cnt = nullptr; d.region_cap = 0; d.defer_hi = 0;
+        // two slices: one read of the records does both -- the second slice's flips wait in per-CTA lists
+        // (in the record buffer the sort has left free) until the first slice is done with the L2
+        const u64 region_cap = ((n + (u64)grid * per_cta - 1) / ((u64)grid * per_cta)) * per_cta;   // records one CTA sees
+        const bool defer = drounds == 2 && !h->no_defer && (u64)grid * region_cap * sizeof(u32) <= h->cap_ev * sizeof(u64) &&
+                           (u64)grid <= h->lookback_words;
+        if (defer) {
+            d.pos_lo = 0; d.pos_hi = (u32)std::min(n, span); d.defer_hi = (u32)n;
+            d.defer_list = reinterpret_cast<u32*>(sorted == h->recB ? h->recC : h->recB);
+            d.defer_cnt = h->lookback; d.region_cap = region_cap;
+            if (carry) diff_flag_kernel<true, true><<<grid, kDiffThreads, 0, st>>>(d);
+            else diff_flag_kernel<false, true><<<grid, kDiffThreads, 0, st>>>(d);
             CK(h, cudaGetLastError());
-            h->n_launches++;
+            diff_apply_kernel<<<grid, 256, 0, st>>>(d.defer_list, d.defer_cnt, region_cap, (u32)grid, h->bitmap);
+            CK(h, cudaGetLastError());
+            h->n_launches += 2;
+            h->n_diff_rounds = 1;
+        } else {
+            h->n_diff_rounds = (u32)drounds;
+            for (u64 r = 0; r < drounds; r++) {
+                d.pos_lo = (u32)(r * span); d.pos_hi = (u32)std::min(n, (r + 1) * span);
+                if (d.pos_lo >= d.pos_hi) break;
+                if (carry) diff_flag_kernel<true, false><<<grid, kDiffThreads, 0, st>>>(d);
+                else diff_flag_kernel<false, false><<<grid, kDiffThreads, 0, st>>>(d);
+                CK(h, cudaGetLastError());
+                h->n_launches++;
+            }
         }
     } else {
         // R-trace: every survivor is emitted; nothing to intern or sort
@@ -657,6 +681,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     CK(h, cudaEventRecord(h->ev[5], st));
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
+    if (dedupe) h->last.n_tombstones = h->last.n_del_survived;      // every DELETED survivor is a tombstone of the T-trace
     int rc = check_flags(h, h->last.flags);
     if (rc) { h->carry_valid = false; return rc; }
     if (h->last.flags & kFlagUnordered) {

@@ -218,6 +218,60 @@ def test_zipf_with_tombstones_digest_100m():
         assert st2["n_emitted"] == st["n_emitted"] and e.digest() == dig
 
 
+# ---- the diff stage's bitmap slices (1 B events need two; PTE_DIFF_ROUND_MB shrinks them for the test) -------
+@pytest.mark.parametrize("mode", ["deferred", "looped", "four_slices"])
+@pytest.mark.parametrize("shape", [
+    dict(dist=0, p_del=0.0),                         # 80 % emitted: the diff clears the suppressed bits
+    dict(dist=1, p_del=0.05, quiet=True),            # almost nothing emitted: the diff sets the emitted bits
+])
+def test_bitmap_slices_give_the_same_answer(monkeypatch, mode, shape):
+    monkeypatch.setenv("PTE_DIFF_ROUND_MB", "1")                       # 8 M positions per slice
+    if mode == "looped":
+        monkeypatch.setenv("PTE_NO_DEFER", "1")
+    n, pods = (30_000_000 if mode == "four_slices" else 12_000_000), 150_000
+    shape = dict(shape)
+    quiet = shape.pop("quiet", False)
+    with PhaseTransitionEngine(n, pods) as e:
+        if quiet:
+            cols = c_oracle.generate(SEED + 9, n, pods, **shape)
+            cols["phase"][:] = po.PH_RUNNING                           # only ADDED-after-DELETED and tombstones get out
+            e.ingest(cols)
+            want, ost, dig = c_oracle.replay(cols, pods_hint=pods)
+        else:
+            e.generate(SEED + 9, n, pods, **shape)
+            ost, dig = c_oracle.generate_replay(SEED + 9, n, pods, **shape)
+        for env in ("staging", "production"):
+            flt = FILTERS[env]
+            e.set_filters(flt["ns_allow"], critical_only=flt["critical_only"])
+            st = e.run()
+            assert st["n_diff_rounds"] == {"deferred": 1, "looped": 2, "four_slices": 4}[mode]
+            if env == "staging":
+                assert {k: st[k] for k in ost} == ost and e.digest() == dig
+                if quiet:
+                    assert np.array_equal(e.fetch(columns=("idx",)).idx.astype(np.uint64), want)
+            else:
+                cols = e.read_log()
+                want_p, ost_p, dig_p = c_oracle.replay(cols, critical_only=True, ns_allow=flt["ns_allow"], pods_hint=pods)
+                assert {k: st[k] for k in ost_p} == ost_p and e.digest() == dig_p
+                assert np.array_equal(e.fetch(columns=("idx",)).idx.astype(np.uint64), want_p)
+
+
+def test_carried_batches_with_deferred_slices(monkeypatch):
+    monkeypatch.setenv("PTE_DIFF_ROUND_MB", "1")
+    n, pods = 24_000_000, 200_000
+    cols = c_oracle.generate(SEED + 10, n, pods, dist=1, p_del=0.05, p_nostatus=0.02)
+    want, ost, _ = c_oracle.replay(cols, pods_hint=pods)
+    got, tomb = [], 0
+    with PhaseTransitionEngine(n // 2, pods) as e:
+        for lo, hi in ((0, n // 2), (n // 2, n)):
+            e.ingest({k: v[lo:hi] for k, v in cols.items()})
+            st = e.run(dedupe=True, carry=True)
+            assert st["n_diff_rounds"] == 1 and st["n_launches"] >= 11
+            got.append(e.fetch(columns=("idx",)).idx.astype(np.int64) + lo)
+            tomb += st["n_tombstones"]
+    assert np.array_equal(np.concatenate(got), want.astype(np.int64)) and tomb == ost["n_tombstones"]
+
+
 # ---- errors are loud -------------------------------------------------------------
 def test_bad_event_is_rejected(eng):
     cols = c_oracle.generate(7, 1000, 10)

@@ -8,6 +8,6 @@ $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_ou
 tail -c 400 gpurun_out/plain.log
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 tail -1 gpurun_out/ncu_list.log
-# warm-up run = 8 kernels after the generator's 6; capture one instance of every kernel of a timed step
-ncu --set full --clock-control none --import-source on -k regex:"intern_pack|radix_pass|diff_flag|diff_sample|bitmap_init|bitmap_count|tile_scan|assemble_bitmap" -s 17 -c 11 -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
+# matched launches: 3 radix passes of the generator + 11 of the warm-up step; then capture the first timed step in order
+ncu --set full --clock-control none --import-source on -k regex:"intern_pack|radix_pass|diff_flag|diff_apply|diff_sample|bitmap_init|bitmap_count|tile_scan|assemble_bitmap" -s 14 -c 11 -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
 tail -1 gpurun_out/ncu_full.log
