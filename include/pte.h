@@ -76,7 +76,7 @@ typedef struct pte_stats {
     float ms_assemble;      /* bitmap scan + compaction in replay order + payload columns */
     float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
     uint32_t n_passes;      /* radix scatter passes run */
-    uint32_t n_diff_rounds; /* diff_flag_kernel launches (position rounds) */
+    uint32_t n_diff_rounds; /* diff_flag_kernel launches (one per bitmap slice; one for two slices when the second is deferred) */
 } pte_stats;
 
 /* Parameters of the synthetic replay log (see "Synthetic replay logs" below). */
