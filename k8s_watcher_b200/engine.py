@@ -171,9 +171,15 @@ class PhaseTransitionEngine:
         self._ck(self._L.pte_json_strings(self._h, which, None, 0, None, 0, C.byref(n)))
         if n.value == 0:
             return []
-        buf = C.create_string_buffer(1 << 20)
         off = np.zeros(n.value + 1, np.uint32)
-        self._ck(self._L.pte_json_strings(self._h, which, buf, len(buf), _ptr(off, C.c_uint32), n.value, C.byref(n)))
+        size = 1 << 20
+        while True:                                   # the ABI has no size query for the text: grow until it fits
+            buf = C.create_string_buffer(size)
+            rc = self._L.pte_json_strings(self._h, which, buf, len(buf), _ptr(off, C.c_uint32), n.value, C.byref(n))
+            if rc != -4 or size >= (1 << 32):         # -4 = PTE_ERR_CAPACITY
+                break
+            size <<= 2
+        self._ck(rc)
         raw = buf.raw
         return [raw[int(off[i]):int(off[i + 1])].decode("utf-8") for i in range(n.value)]
 

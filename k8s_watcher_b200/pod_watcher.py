@@ -120,7 +120,7 @@ class PodWatcher:
     def __init__(self, environment: str = "development", *, dedupe: bool = True,
                  sink: Optional[ClusterApiClient] = None, engine: Optional[PhaseTransitionEngine] = None,
                  device: int = 0, config_dir: str = "config", flush_every: Optional[int] = None,
-                 max_pods: int = 1 << 20):
+                 max_pods: int = 1 << 20, keep_batches: Optional[int] = None):
         self.environment = environment
         self.config_dir = config_dir           # CWD-relative by default, like upstream (:22,:25)
         self.config = self._load_environment_config()
@@ -132,7 +132,10 @@ class PodWatcher:
         self._engine = engine
         self._device = device
         self._pending: List[Dict[str, Any]] = []
+        # every replay's result, oldest first; a watcher that runs for days sets keep_batches so that only the
+        # last few (each holds its log) stay alive
         self.batches: List[Batch] = []
+        self.keep_batches = keep_batches
         # live loop: replay every `flush_every` queued events as one batch of a stream; the engine carries the
         # uid dictionary and each pod's last known phase from batch to batch (None: one replay at stream end)
         self.flush_every = flush_every
@@ -295,8 +298,13 @@ class PodWatcher:
         stats = eng.run(dedupe=dedupe, carry=carry)
         # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
-        self.batches.append(batch)
+        self._remember(batch)
         return batch
+
+    def _remember(self, batch: Batch) -> None:
+        self.batches.append(batch)
+        if self.keep_batches is not None and len(self.batches) > max(1, self.keep_batches):
+            del self.batches[:len(self.batches) - max(1, self.keep_batches)]
 
     def replay_watch_json(self, text: bytes, *, dedupe: Optional[bool] = None, max_events: int = 0, max_pods: int = 0) -> Batch:
         """Replay a raw watch log (newline-delimited JSON watch events, what ``for event in stream`` would have
@@ -309,7 +317,7 @@ class PodWatcher:
         eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
         stats = eng.run(dedupe=dedupe)
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
-        self.batches.append(batch)
+        self._remember(batch)
         return batch
 
     def flush(self) -> Optional[Batch]:
