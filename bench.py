@@ -274,13 +274,16 @@ def main():
         ach = nbytes / (ms * 1e-3) / 1e9
         by_kernel[name] = {"launches_per_step": per_step, "avg_launch_ms": ms, "algorithmic_bytes_per_launch": nbytes,
                            "achieved": ach, "frac": ach / peak, "share_of_step": per_step * ms / avg["ms_total"],
-                           "traffic": traffic.get(name)}
+                           "traffic": traffic.get(name),
+                           # real DRAM bytes (ncu capture of the same workload) over the live launch time
+                           "traffic_frac": (traffic[name] / (ms * 1e-3) / 1e9 / peak) if traffic.get(name) else None}
     dom = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"]) if by_kernel else None
     roof = None
     if dom:
         d = by_kernel[dom]
         roof = {"bound": "hbm", "kernel": dom, "achieved": d["achieved"], "peak": peak, "unit": "GB/s", "frac": d["frac"],
-                "peak_source": peak_src, "traffic": d["traffic"], "launches_per_step": d["launches_per_step"],
+                "peak_source": peak_src, "traffic": d["traffic"], "traffic_frac": d["traffic_frac"],
+                "launches_per_step": d["launches_per_step"],
                 "avg_launch_ms": d["avg_launch_ms"], "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                 "share_of_step": d["share_of_step"], "frac_of_8TBps_nominal": d["achieved"] / 8000.0,
                 # the whole step against its algorithmic bytes and against the compulsory I/O (30 B in + 16 B per emitted record)

@@ -629,9 +629,11 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         d.defer_list = nullptr; d.defer_cnt = nullptr; d.region_cap = 0; d.defer_hi = 0;
         // two slices: one read of the records does both -- the second slice's flips wait in per-CTA lists
         // (in the record buffer the sort has left free) until the first slice is done with the L2
-        const u64 region_cap = ((n + (u64)grid * per_cta - 1) / ((u64)grid * per_cta)) * per_cta;   // records one CTA sees
-        const bool defer = drounds == 2 && !h->no_defer && (u64)grid * region_cap * sizeof(u32) <= h->cap_ev * sizeof(u64) &&
-                           (u64)grid <= h->lookback_words;
+        const u64 per_warp = 32ull * kDiffPerThread;
+        const u64 n_lists = (u64)grid * (kDiffThreads / 32);
+        const u64 region_cap = ((n + (u64)grid * per_cta - 1) / ((u64)grid * per_cta)) * per_warp;   // records one warp sees
+        const bool defer = drounds == 2 && !h->no_defer && n_lists * region_cap * sizeof(u32) <= h->cap_ev * sizeof(u64) &&
+                           n_lists <= h->lookback_words;
         if (defer) {
             d.pos_lo = 0; d.pos_hi = (u32)std::min(n, span); d.defer_hi = (u32)n;
             d.defer_list = reinterpret_cast<u32*>(sorted == h->recB ? h->recC : h->recB);
@@ -639,7 +641,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             if (carry) diff_flag_kernel<true, true><<<grid, kDiffThreads, 0, st>>>(d);
             else diff_flag_kernel<false, true><<<grid, kDiffThreads, 0, st>>>(d);
             CK(h, cudaGetLastError());
-            diff_apply_kernel<<<grid, 256, 0, st>>>(d.defer_list, d.defer_cnt, region_cap, (u32)grid, h->bitmap);
+            diff_apply_kernel<<<grid, 256, 0, st>>>(d.defer_list, d.defer_cnt, region_cap, (u32)n_lists, h->bitmap);
             CK(h, cudaGetLastError());
             h->n_launches += 2;
             h->n_diff_rounds = 1;

@@ -371,19 +371,22 @@ bitmap_init_kernel(u32* __restrict__ bitmap, const u32* __restrict__ keep, u64 n
 // rounds and the threads of one round cannot see each other's updates.
 // DEFER: the launch covers two slices of the position space with ONE read of the records.  Flips in
 // [pos_lo, pos_hi) go straight to the bitmap; flips in [pos_hi, defer_hi) are appended to a list private to
-// the CTA (positions, 4 bytes each, in a record buffer the sort no longer needs; one warp scan and one
-// shared-memory atomic per 128 records) and diff_apply_kernel plays them back afterwards, when that slice of
-// the bitmap can have the L2 to itself.  (Lists private to a thread need no scan, but their 4-byte appends
+// the warp (positions, 4 bytes each, in a record buffer the sort no longer needs; one warp scan per 128
+// records, the cursor lives in a register) and diff_apply_kernel plays them back afterwards, when that slice
+// of the bitmap can have the L2 to itself.  (Lists private to a thread need no scan, but their 4-byte appends
 // turn into read-modify-write traffic in DRAM: measured 4.4 ms against 3.7 ms for two plain rounds.)
 // Every DELETED survivor is emitted, so the tombstone count is the DELETED count intern_pack_kernel took.
 struct DiffArgs {
     const u64* in; const u64* n_ptr;
     u32* bitmap; RecLayout L; Counters* ctr;
     u32 pos_lo, pos_hi, defer_hi;
-    u32* defer_list; u32* defer_cnt; u64 region_cap;     // DEFER: region_cap entries per CTA
+    u32* defer_list; u32* defer_cnt; u64 region_cap;     // DEFER: region_cap entries per warp
     const u8* state_old; u8* state_new;                 // CARRY
 };
-static constexpr int kDiffPerThread = 4, kDiffThreads = 256;
+#ifndef PTE_DIFF_PER_THREAD
+#define PTE_DIFF_PER_THREAD 8      // measured on B200, diff stage of 1 B records: 2/4/8/12/16 -> 5.08/3.52/2.92/2.82/3.10 ms
+#endif
+static constexpr int kDiffPerThread = PTE_DIFF_PER_THREAD, kDiffThreads = 256;      // records per thread and iteration (even)
 
 // A position is flipped at most once per run (one record per position), so XOR serves both polarities.
 // Plain RED: keeps the compiler from wrapping the atomic in its warp-aggregation sequence (two flips of one
@@ -403,26 +406,26 @@ __global__ void __launch_bounds__(kDiffThreads) diff_flag_kernel(DiffArgs a) {
     const u32 idx_mask = (u32)a.L.idx_mask();
     const u32 span = a.pos_hi - a.pos_lo, span_all = (DEFER ? a.defer_hi : a.pos_hi) - a.pos_lo;
     const bool invert = a.ctr->invert != 0;
-    __shared__ u32 s_cnt;
-    if (DEFER) {
-        if (threadIdx.x == 0) s_cnt = 0;
-        __syncthreads();
-    }
-    u32* const my_list = DEFER ? a.defer_list + (u64)blockIdx.x * a.region_cap : nullptr;
+    const u64 gwarp = ((u64)blockIdx.x * kDiffThreads + threadIdx.x) >> 5;
+    u32* tail = DEFER ? a.defer_list + gwarp * a.region_cap : nullptr;     // end of this warp's list (same in all lanes)
     const u64 stride = (u64)gridDim.x * kDiffThreads * kDiffPerThread;
     // the loop bound is warp-uniform (wb = first record of the warp) so that every lane reaches the shuffles
     for (u64 wb = ((u64)blockIdx.x * kDiffThreads + (threadIdx.x & ~31u)) * kDiffPerThread; wb < n; wb += stride) {
         const u64 i = wb + lane * kDiffPerThread;
         const ulonglong2* src = reinterpret_cast<const ulonglong2*>(a.in + i);      // padded: readable past n
-        const ulonglong2 c0 = __ldcs(src), c1 = __ldcs(src + 1);
-        u64 p = __shfl_up_sync(0xffffffffu, c1.y, 1);
-        if (lane == 0) p = i > 0 ? a.in[i - 1] : ~c0.x;                             // ~c0.x: a different key
-        u64 nxt = 0;
-        if (CARRY) {
-            nxt = __shfl_down_sync(0xffffffffu, c0.x, 1);
-            if (lane == 31) nxt = a.in[i + kDiffPerThread];
+        u64 r[kDiffPerThread + 1];
+#pragma unroll
+        for (int k = 0; k < kDiffPerThread / 2; k++) {
+            const ulonglong2 c = __ldcs(src + k);
+            r[2 * k] = c.x; r[2 * k + 1] = c.y;
         }
-        const u64 r[5] = {c0.x, c0.y, c1.x, c1.y, nxt};
+        u64 p = __shfl_up_sync(0xffffffffu, r[kDiffPerThread - 1], 1);
+        if (lane == 0) p = i > 0 ? a.in[i - 1] : ~r[0];                             // ~r[0]: a different key
+        r[kDiffPerThread] = 0;
+        if (CARRY) {
+            r[kDiffPerThread] = __shfl_down_sync(0xffffffffu, r[0], 1);
+            if (lane == 31) r[kDiffPerThread] = a.in[i + kDiffPerThread];
+        }
         const u32 left = i >= n ? 0u : (n - i >= (u64)kDiffPerThread ? (u32)kDiffPerThread : (u32)(n - i));   // records of this lane
         u32 dpos[kDiffPerThread], dmask = 0;
 #pragma unroll
@@ -447,7 +450,7 @@ __global__ void __launch_bounds__(kDiffThreads) diff_flag_kernel(DiffArgs a) {
             p = cur;
         }
         if (DEFER) {
-            // append this warp's deferred positions behind the CTA's cursor
+            // append this warp's deferred positions to its list
             const u32 c = __popc(dmask);
             u32 incl = c;
 #pragma unroll
@@ -455,21 +458,14 @@ __global__ void __launch_bounds__(kDiffThreads) diff_flag_kernel(DiffArgs a) {
                 const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
                 if (lane >= (u32)d) incl += t;
             }
-            const u32 total = __shfl_sync(0xffffffffu, incl, 31);
-            if (total) {                                   // warp-uniform
-                u32 base = 0;
-                if (lane == 31) asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(base) : "r"((u32)__cvta_generic_to_shared(&s_cnt)), "r"(total) : "memory");
-                u32 off = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+            u32* q = tail + (incl - c);
 #pragma unroll
-                for (int k = 0; k < kDiffPerThread; k++)
-                    if ((dmask >> k) & 1u) my_list[off++] = dpos[k];
-            }
+            for (int k = 0; k < kDiffPerThread; k++)
+                if ((dmask >> k) & 1u) *q++ = dpos[k];
+            tail += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
-    if (DEFER) {
-        __syncthreads();
-        if (threadIdx.x == 0) a.defer_cnt[blockIdx.x] = s_cnt;
-    }
+    if (DEFER && lane == 0) a.defer_cnt[gwarp] = (u32)(tail - (a.defer_list + gwarp * a.region_cap));
 }
 
 // Plays the deferred flips back: list r holds cnt[r] positions.
