@@ -87,6 +87,29 @@ __device__ __forceinline__ ulonglong2 ld_slot(const Slot* p, u64 pol) {
 // and then the 128-bit CAS -- which returns the true content -- decides.
 // `v` is the content of slot `sl` as loaded by the caller (so that a thread can have the first
 // probe of all its events in flight before it resolves any of them).
+// p-th slot of the probe sequence that starts at `home`.  The sequence walks the eight slots of home's
+// 128-byte line cyclically before it moves on to the next line (same offset), because a probe that misses
+// L2 brings in the whole line (profiles/r01_gather/): a probe run then leaves its first line only when the
+// line is full.  PTE_PROBE_LINE=0 is plain linear probing.
+#ifndef PTE_PROBE_LINE
+#define PTE_PROBE_LINE 1
+#endif
+__device__ __forceinline__ u32 probe_slot(u32 home, u32 p, u32 mask) {
+#if PTE_PROBE_LINE
+    return ((((home >> 3) + (p >> 3)) << 3) | ((home + p) & 7u)) & mask;
+#else
+    return (home + p) & mask;
+#endif
+}
+// the same sequence, stepped: slot p from slot p-1 (needs no copy of `home` in a register)
+__device__ __forceinline__ u32 probe_next(u32 sl, u32 p, u32 mask) {
+#if PTE_PROBE_LINE
+    return (((sl & ~7u) + ((p & 7u) == 0 ? 8u : 0u)) | ((sl + 1) & 7u)) & mask;
+#else
+    return (sl + 1) & mask;
+#endif
+}
+
 __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u64 hi, u64 lo, u32 sl, ulonglong2 v,
                                           u32& inserted, u32* __restrict__ flags, u64 pol) {
     for (int p = 0; p < kMaxProbe; ++p) {
@@ -97,7 +120,7 @@ __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u6
         } else if (v.x == hi && v.y == lo) {
             return sl;
         }
-        sl = (sl + 1) & mask;
+        sl = probe_next(sl, p + 1, mask);
         v = ld_slot(table + sl, pol);
     }
     atomicOr(flags, kFlagTableFull);
@@ -498,13 +521,13 @@ key_lookup_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict_
     for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
         const u32 i = out_idx[j];
         const u64 hi = uid_hi[i], lo = uid_lo[i];
-        u32 sl = uid_home_slot(hi, lo, mask);
+        const u32 home = uid_home_slot(hi, lo, mask);
         u64 key = ~0ull;
         for (int p = 0; p < kMaxProbe; ++p) {
+            const u32 sl = probe_slot(home, p, mask);
             ulonglong2 v = *reinterpret_cast<const ulonglong2*>(table + sl);
             if (v.x == hi && v.y == lo) { key = sl; break; }
             if ((v.x | v.y) == 0) break;
-            sl = (sl + 1) & mask;
         }
         out_key[j] = key;
     }
