@@ -44,42 +44,43 @@ __device__ __forceinline__ u64 probe(const ulonglong2* t, u64 slot, u64 pol) {
     return v.x ^ v.y;
 }
 
-template <int MODE>
+template <int MODE, int ILP = 4>
 __global__ void __launch_bounds__(256) gather(const ulonglong2* __restrict__ t, u64 slots, u64 per_thread, u64 seed, u64* out) {
     u64 pol = 0;
     if (MODE == EVICT_FIRST16) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     if (MODE == EVICT_LAST16) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     u64 acc = 0;
-    for (u64 i = 0; i < per_thread; i += 4) {
-        u64 s[4];
+    for (u64 i = 0; i < per_thread; i += ILP) {
+        u64 s[ILP];
 #pragma unroll
-        for (int k = 0; k < 4; k++) s[k] = __umul64hi(mix64(seed + (gid * per_thread + i + k) * 0x9E3779B97F4A7C15ull), slots);
-        u64 v[4];
+        for (int k = 0; k < ILP; k++) s[k] = __umul64hi(mix64(seed + (gid * per_thread + i + k) * 0x9E3779B97F4A7C15ull), slots);
+        u64 v[ILP];
 #pragma unroll
-        for (int k = 0; k < 4; k++) v[k] = probe<MODE>(t, s[k], pol);
-        acc += v[0] ^ v[1] ^ v[2] ^ v[3];
+        for (int k = 0; k < ILP; k++) v[k] = probe<MODE>(t, s[k], pol);
+#pragma unroll
+        for (int k = 0; k < ILP; k++) acc += v[k];
     }
     if (acc == 0x1234567ull) out[0] = acc;      // keeps the loads alive
 }
 
-template <int MODE>
-void run(const ulonglong2* t, u64 slots, u64* out) {
-    const int blocks = 148 * 8;
+template <int MODE, int ILP = 4>
+void run(const ulonglong2* t, u64 slots, u64* out, int ctas_per_sm = 8) {
+    const int blocks = 148 * ctas_per_sm;
     const u64 per_thread = 1024;
     const u64 loads = (u64)blocks * 256 * per_thread;
-    gather<MODE><<<blocks, 256>>>(t, slots, per_thread, 1, out);
+    gather<MODE, ILP><<<blocks, 256>>>(t, slots, per_thread, 1, out);
     cudaDeviceSynchronize();
     cudaEvent_t a, b;
     cudaEventCreate(&a); cudaEventCreate(&b);
     cudaEventRecord(a);
-    gather<MODE><<<blocks, 256>>>(t, slots, per_thread, 2, out);
+    gather<MODE, ILP><<<blocks, 256>>>(t, slots, per_thread, 2, out);
     cudaEventRecord(b);
     cudaEventSynchronize(b);
     float ms = 0;
     cudaEventElapsedTime(&ms, a, b);
     const double bytes = MODE == PLAIN8 ? 8 : (MODE == PAIR32 ? 32 : 16);
-    printf("  %-26s %8.3f ms  %7.2f G loads/s  %7.1f GB/s useful\n", kNames[MODE], ms, loads / ms * 1e-6, loads * bytes / ms * 1e-6);
+    printf("  %-26s ilp %2d x %d CTAs/SM %8.3f ms  %7.2f G loads/s  %7.1f GB/s useful\n", kNames[MODE], ILP, ctas_per_sm, ms, loads / ms * 1e-6, loads * bytes / ms * 1e-6);
 }
 
 int main(int argc, char** argv) {
@@ -101,6 +102,11 @@ int main(int argc, char** argv) {
     cudaMemset(t, 1, slots * 16);
     printf("table %llu MB (%llu slots of 16 B), %d x 256 threads, 4 loads in flight per thread\n", slots * 16 >> 20, slots, 148 * 8);
     run<PLAIN16>(t, slots, out);
+    if (argc > 3 && argv[3][0] == 'i') {                       // loads in flight: per thread x CTAs per SM
+        run<PLAIN16, 1>(t, slots, out); run<PLAIN16, 2>(t, slots, out); run<PLAIN16, 8>(t, slots, out); run<PLAIN16, 16>(t, slots, out);
+        run<PLAIN16, 4>(t, slots, out, 2); run<PLAIN16, 4>(t, slots, out, 4); run<PLAIN16, 4>(t, slots, out, 5);
+        run<PLAIN16, 8>(t, slots, out, 4); run<PLAIN16, 16>(t, slots, out, 2);
+    }
     if (argc > 3) { cudaDeviceSynchronize(); return 0; }      // size sweeps: the plain load only
     run<CG16>(t, slots, out);
     run<CV16>(t, slots, out);
