@@ -473,6 +473,15 @@ def test_live_loop_micro_batches_match_one_replay(monkeypatch):
         want = dict(fx["payloads"][k])
         b.pop("event_timestamp"), want.pop("event_timestamp")
         assert b == want
+    # a watcher that only keeps its last two batches alive notifies exactly the same
+    _k8s_stub.queue_events(events)
+    fk.set_stream(events)
+    sink2 = ClusterApiClient("http://clusterapi.invalid")
+    w2 = PodWatcher("staging", sink=sink2, flush_every=64, max_pods=64, keep_batches=2)
+    w2.environment, w2.config = "development", cfg
+    w2.start_watching()
+    assert len(w2.batches) == 2
+    assert [json.loads(x)["uid"] for x in sink2.transport.bodies()] == [x["uid"] for x in bodies]
 
 
 # ---- payload serialisation on the device ------------------------------------------
