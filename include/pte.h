@@ -77,6 +77,12 @@ typedef struct pte_stats {
     float ms_pass_avg;      /* mean duration of one radix scatter pass (the dominant kernel) */
     uint32_t n_passes;      /* radix scatter passes run */
     uint32_t n_diff_rounds; /* diff_flag_kernel launches (one per bitmap slice; one for two slices when the second is deferred) */
+    uint32_t path;          /* 0: sort path (intern, radix sort, adjacent diff); 1: partition-first path (large one-shot T-trace runs).
+                               On path 1 ms_intern = partition counts + scatter, ms_sort_key = 0, ms_diff = replay of the partitions */
+    uint32_t n_pending;     /* path 1: events resolved by the cross-segment fix-up (cut partitions only) */
+    float ms_part_hist;     /* path 1: uid hash -> partition counts + replay-order check + segment table */
+    float ms_part_scatter;  /* path 1: stable scatter of the events into 24-byte partition records */
+    float ms_part_replay;   /* path 1: in-order replay of every partition against shared-memory state (+ fix-up) */
 } pte_stats;
 
 /* Parameters of the synthetic replay log (see "Synthetic replay logs" below). */

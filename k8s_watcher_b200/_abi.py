@@ -28,7 +28,8 @@ class PteStats(C.Structure):
         ("n_pods", C.c_uint64), ("ordered", C.c_uint32), ("n_launches", C.c_uint32),
         ("ms_total", C.c_float), ("ms_intern", C.c_float), ("ms_sort_key", C.c_float), ("ms_diff", C.c_float),
         ("ms_sort_order", C.c_float), ("ms_assemble", C.c_float), ("ms_pass_avg", C.c_float),
-        ("n_passes", C.c_uint32), ("n_diff_rounds", C.c_uint32),
+        ("n_passes", C.c_uint32), ("n_diff_rounds", C.c_uint32), ("path", C.c_uint32), ("n_pending", C.c_uint32),
+        ("ms_part_hist", C.c_float), ("ms_part_scatter", C.c_float), ("ms_part_replay", C.c_float),
     ]
 
     def as_dict(self):

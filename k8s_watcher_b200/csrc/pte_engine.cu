@@ -3,6 +3,7 @@
 // -> handle_pod_event (:214-241), plus the last-known-phase layer of SURVEY.md 8a row 7.
 #include "../../include/pte.h"
 #include "pte_kernels.cuh"
+#include "pte_partition.cuh"
 #include "pte_json.cuh"
 
 #include <dlfcn.h>
@@ -86,7 +87,21 @@ struct pte_engine {
     u64 table_cap = 0;
     RecLayout L{};
     // sort
+    u64* rec_pool = nullptr;                                 // 3 x cap_ev words: recA | recB | recC, or the 24-byte partition records
     u64 *recA = nullptr, *recB = nullptr, *recC = nullptr;   // interned records (round-major) + sort ping-pong
+    // partition-first replay (pte_partition.cuh)
+    u64 table_alloc = 0;                                     // slots allocated (>= table_cap, >= kParts * part_slice)
+    u32 part_slice = 0;                                      // dictionary slots per partition
+    u32 *part_hist = nullptr, *part_start = nullptr, *part_nsegs = nullptr;
+    Segment* segs = nullptr;
+    u8* seg_export = nullptr;
+    u64 part_min_events = ~0ull;                             // auto mode: logs at least this long take the partition path (PTE_PART_MIN); off until it wins
+    u32 seg_q8 = 304;                                        // segment length in 1/256 of the mean partition (PTE_SEG_Q8)
+    int path_mode = 0;                                       // PTE_PATH: 0 auto, 1 always sort, 2 always partition
+    bool force_sort = false;                                 // one run: the partitioned attempt overflowed something
+    int last_path = 0;                                       // path of the last run (0 sort, 1 partition)
+    int replay_occ = 1, scatter_smem = 0, replay_smem = 0;
+    int scatter_cfg = 0, scatter_occ = 1, scatter_tile = 6144, scatter_threads = 512;
     u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
     u8 *state_old = nullptr, *state_new = nullptr;           // per dictionary slot: last known phase of the stream
     bool carry_valid = false;                                // dictionary + state hold a stream that can be continued
@@ -251,6 +266,106 @@ int check_flags(pte_engine* h, u32 flags) {
     return PTE_OK;
 }
 
+// partition scatter configurations (threads, records per thread, CTAs per SM); PTE_SCATTER_CFG picks one for tuning runs
+#define PTE_FOR_EACH_SCATTER_CFG(X) X(0, 512, 12, 1) X(1, 256, 12, 2) X(2, 256, 8, 3) X(3, 512, 8, 1)
+
+template <int T, int I, int B>
+cudaError_t prepare_scatter(pte_engine* h) {
+    h->scatter_smem = (int)sizeof(ScatterSmem<T, I>);
+    h->scatter_tile = T * I; h->scatter_threads = T;
+    cudaError_t e = cudaFuncSetAttribute(part_scatter_kernel<T, I, B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->scatter_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(part_scatter_kernel<T, I, B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->scatter_smem);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->scatter_occ, part_scatter_kernel<T, I, B, false>, T, h->scatter_smem);
+    return e;
+}
+template <int T, int I, int B>
+cudaError_t launch_scatter(pte_engine* h, int grid, bool filtered, const ScatterArgs& sa) {
+    if (filtered) part_scatter_kernel<T, I, B, true><<<grid, T, h->scatter_smem, h->stream>>>(sa);
+    else part_scatter_kernel<T, I, B, false><<<grid, T, h->scatter_smem, h->stream>>>(sa);
+    return cudaGetLastError();
+}
+
+int prepare_partition(pte_engine* h) {
+    h->replay_smem = kRpStages * kRpBufRecs * 24 + (int)((h->part_slice + 15) & ~15u) + (int)sizeof(ReplaySmemFixed);
+    cudaError_t e = cudaErrorInvalidValue;
+    switch (h->scatter_cfg) {
+#define X(id, T, I, B) case id: e = prepare_scatter<T, I, B>(h); break;
+        PTE_FOR_EACH_SCATTER_CFG(X)
+#undef X
+    }
+    if (e == cudaSuccess && h->scatter_occ < 1) e = cudaErrorInvalidConfiguration;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(part_replay_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->replay_smem);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->replay_occ, part_replay_kernel, kRpThreads, h->replay_smem);
+    if (e != cudaSuccess) FAIL(h, PTE_ERR_CUDA, std::string("partition path set-up: ") + cudaGetErrorString(e));
+    if (h->replay_occ < 1) h->path_mode = 1;      // the state bytes of one partition do not fit in shared memory: sort path only
+    return PTE_OK;
+}
+
+// The T-trace of the resident log by the partition-first path: fills the emit bitmap (and keepmap when filtered).
+// Events ev[6] (after the counts), ev[1] (after the scatter), ev[7] (before the replay) and ev[3] are recorded here.
+int run_partitioned(pte_engine* h, const InternArgs& a, bool filtered) {
+    cudaStream_t st = h->stream;
+    const u64 n = h->n_events;
+    const u32 NS = h->part_slice;
+    if (!h->seg_export) CK(h, cudaMalloc((void**)&h->seg_export, (u64)kMaxSegments * NS));
+    CK(h, cudaMemsetAsync(h->part_hist, 0, sizeof(u32) * kParts, st));
+    if (filtered) {
+        int fgrid = (int)std::min<u64>((n / 4 + 255) / 256 + 1, (u64)h->num_sms * 16);
+        filter_flag_kernel<<<fgrid, 256, 0, st>>>(a, h->keepmap);
+        CK(h, cudaGetLastError());
+        h->n_launches++;
+    }
+    PartHistArgs ha{h->uid_lo, h->rv, h->keepmap, n, h->part_hist, h->ctr};
+    int hgrid = (int)std::min<u64>((n / 4 + 255) / 256 + 1, (u64)h->num_sms * 8);
+    if (filtered) part_hist_kernel<true><<<hgrid, 256, 0, st>>>(ha);
+    else part_hist_kernel<false><<<hgrid, 256, 0, st>>>(ha);
+    CK(h, cudaGetLastError());
+    part_scan_kernel<<<1, kParts, 0, st>>>(h->part_hist, h->part_start, h->segs, h->part_nsegs, h->ctr, h->seg_q8, filtered ? 0 : 1);
+    CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev[6], st));
+    const u64 tiles = (n + h->scatter_tile - 1) / h->scatter_tile;
+    if (tiles * kParts > h->lookback_words) FAIL(h, PTE_ERR_CAPACITY, "look-back buffer too small");
+    CK(h, cudaMemsetAsync(h->lookback, 0, tiles * kParts * sizeof(u32), st));
+    ScatterArgs sa{h->uid_hi, h->uid_lo, h->phase, h->type, h->keepmap, n, h->part_start, h->rec_pool, h->lookback,
+                   &h->ctr->ticket[2], h->ctr};
+    int sgrid = (int)std::min<u64>(tiles, (u64)h->num_sms * h->scatter_occ);
+    {
+        cudaError_t e = cudaErrorInvalidValue;
+        switch (h->scatter_cfg) {
+#define X(id, T, I, B) case id: e = launch_scatter<T, I, B>(h, sgrid, filtered, sa); break;
+            PTE_FOR_EACH_SCATTER_CFG(X)
+#undef X
+        }
+        CK(h, e);
+    }
+    CK(h, cudaEventRecord(h->ev[1], st));
+    CK(h, cudaEventRecord(h->ev[2], st));
+    // polarity of the bitmap from a sample replay (a prefix of four partitions, no side effects but dictionary entries)
+    ReplayArgs ra;
+    ra.rec = h->rec_pool; ra.segs = h->segs + kMaxSegments; ra.n_segs = h->part_nsegs + 1; ra.ticket = &h->ctr->ticket[3];
+    ra.first_seg = kMaxSegments; ra.table = h->table; ra.slice_slots = NS; ra.bitmap = h->bitmap; ra.ctr = h->ctr;
+    ra.seg_export = h->seg_export; ra.pending = reinterpret_cast<PendingHead*>(h->out_key);
+    ra.pending_cap = (u32)std::min<u64>(h->cap_ev / 2, 0xFFFFFFFFull); ra.count_only = 1;
+    const bool sample = !h->no_invert;
+    if (sample) {
+        part_replay_kernel<<<kSampleSegments, kRpThreads, h->replay_smem, st>>>(ra);
+        CK(h, cudaGetLastError());
+        CK(h, cudaMemsetAsync(&h->ctr->ticket[3], 0, sizeof(u32), st));
+        h->n_launches++;
+    }
+    bitmap_init_kernel<<<(int)std::min<u64>(((n + 31) / 32 + 255) / 256, (u64)h->num_sms * 8), 256, 0, st>>>(
+        h->bitmap, filtered ? h->keepmap : nullptr, n, h->ctr, sample ? 1 : 0);
+    CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev[7], st));
+    ra.segs = h->segs; ra.n_segs = h->part_nsegs; ra.first_seg = 0; ra.count_only = 0;
+    part_replay_kernel<<<h->num_sms * h->replay_occ, kRpThreads, h->replay_smem, st>>>(ra);
+    CK(h, cudaGetLastError());
+    pending_fixup_kernel<<<h->num_sms * 4, 256, 0, st>>>(ra.pending, ra.pending_cap, h->segs, h->seg_export, NS, h->bitmap, h->ctr);
+    CK(h, cudaGetLastError());
+    h->n_launches += 6;
+    return PTE_OK;
+}
+
 // Bring a log whose rv decreases somewhere into replay order (ascending rv, ties by arrival) in shadow
 // columns, run the pipeline on those, map the emitted indices back to arrival indices.
 int run_reordered(pte_engine* h, int flags, pte_stats* out) {
@@ -321,7 +436,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->recA, h->recB, h->recC, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->rec_pool, h->part_hist, h->part_start, h->part_nsegs, h->segs, h->seg_export, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
                     h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
@@ -361,6 +476,10 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     if (const char* ni = getenv("PTE_NO_INVERT")) h->no_invert = atoi(ni) != 0;
     if (const char* nd = getenv("PTE_NO_DEFER")) h->no_defer = atoi(nd) != 0;
     if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
+    if (const char* sc = getenv("PTE_SCATTER_CFG")) h->scatter_cfg = std::min(std::max(atoi(sc), 0), 3);
+    if (const char* pm = getenv("PTE_PART_MIN")) h->part_min_events = (u64)atof(pm);
+    if (const char* sq = getenv("PTE_SEG_Q8")) h->seg_q8 = (u32)std::min(std::max(atoi(sq), 32), 4096);
+    if (const char* pp = getenv("PTE_PATH")) h->path_mode = !strcmp(pp, "sort") ? 1 : (!strcmp(pp, "partition") ? 2 : 0);
     const char* cfg = getenv("PTE_PASS_CFG");
     if (cfg) h->pass_cfg = std::min(std::max(atoi(cfg), 0), kNumPassCfgs - 1);
 
@@ -388,13 +507,21 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     const u64 c = h->cap_ev;
     CKC(dev_alloc(h, &h->uid_hi, c)); CKC(dev_alloc(h, &h->uid_lo, c)); CKC(dev_alloc(h, &h->rv, c));
     CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
-    CKC(dev_alloc(h, &h->table, h->table_cap));
+    // the partition-first path views the dictionary as kParts slices of part_slice slots (at least 256 each)
+    h->part_slice = (u32)std::max<u64>(256, h->table_cap / kParts);
+    h->table_alloc = std::max<u64>(h->table_cap, (u64)kParts * h->part_slice);
+    CKC(dev_alloc(h, &h->table, h->table_alloc));
     CKC(dev_alloc(h, &h->state_old, h->table_cap)); CKC(dev_alloc(h, &h->state_new, h->table_cap));
-    CKC(dev_alloc(h, &h->recA, c)); CKC(dev_alloc(h, &h->recB, c)); CKC(dev_alloc(h, &h->recC, c));
+    CKC(dev_alloc(h, &h->rec_pool, 3 * c));
+    h->recA = h->rec_pool; h->recB = h->rec_pool + c; h->recC = h->rec_pool + 2 * c;
+    CKC(dev_alloc(h, &h->part_hist, (u64)kParts)); CKC(dev_alloc(h, &h->part_start, (u64)kParts + 1));
+    CKC(dev_alloc(h, &h->part_nsegs, 2)); CKC(dev_alloc(h, &h->segs, (u64)kMaxSegments + kSampleSegments));
+    CKC(prepare_partition(h));
     CKC(dev_alloc(h, &h->bitmap, c / 32)); CKC(dev_alloc(h, &h->keepmap, c / 32));
     // look-back words: one per (radix tile, digit); also one per intern tile
     u64 min_tile = 2048;
     h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
+    h->lookback_words = std::max<u64>(h->lookback_words, (c / 2048 + 1) * kParts);      // partition scatter: one word per (tile, partition)
     CKC(dev_alloc(h, &h->lookback, h->lookback_words));
     CKC(dev_alloc(h, &h->hist, (u64)kMaxPasses * kRadix));
     CKC(dev_alloc(h, &h->ctr, 1));
@@ -557,8 +684,11 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     cudaStream_t st = h->stream;
     CK(h, cudaEventRecord(h->ev[0], st));
     const bool fresh = !(carry && h->carry_valid);       // start from an empty dictionary
+    // large one-shot T-trace replays take the partition-first path (pte_partition.cuh); streams and short logs the sort path
+    const bool use_part = dedupe && !carry && n && !h->force_sort && h->path_mode != 1 &&
+                          (h->path_mode == 2 || n >= h->part_min_events);
     if (fresh) {
-        CK(h, cudaMemsetAsync(h->table, 0, h->table_cap * sizeof(Slot), st));
+        CK(h, cudaMemsetAsync(h->table, 0, (use_part ? (u64)kParts * h->part_slice : h->table_cap) * sizeof(Slot), st));
         if (carry) CK(h, cudaMemsetAsync(h->state_old, 0, h->table_cap, st));
         h->pods_total = 0;
     }
@@ -572,7 +702,10 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     a.critical_only = h->critical_only; a.ctr = h->ctr; a.keep = h->keepmap; a.block_off = h->lookback;
     a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
     const u64* n_surv_ptr = &h->ctr->n_survived;
-    if (n && dedupe) {
+    if (use_part) {
+        int rc = run_partitioned(h, a, filtered);
+        if (rc) return rc;
+    } else if (n && dedupe) {
         CK(h, cudaMemsetAsync(h->hist, 0, sizeof(u32) * kMaxPasses * kRadix, st));
         const u64 tiles = (n + kInternTile - 1) / kInternTile;
         if (filtered) {
@@ -595,14 +728,16 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         CK(h, cudaGetLastError());
         h->n_launches++;
     }
-    CK(h, cudaEventRecord(h->ev[1], st));
+    if (!use_part) CK(h, cudaEventRecord(h->ev[1], st));
     AssembleArgs as;
     as.n = n; as.bitmap = h->bitmap;
     as.rv = h->rv; as.ns = h->ns; as.phase = h->phase; as.type = h->type;
     as.ctr = h->ctr; as.lookback = h->lookback;
     as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_ns = h->out_ns;
     as.out_phase = h->out_phase; as.out_type = h->out_type;
-    if (n && dedupe) {
+    if (use_part) {
+        // run_partitioned has filled the emit bitmap and recorded ev[1], ev[2]
+    } else if (n && dedupe) {
         u64* sorted = nullptr;
         int rc = sort_field(h, h->recA, h->recB, h->recC, n_surv_ptr, n, h->L.key_shift(),
                             h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
@@ -684,6 +819,15 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
     if (dedupe) h->last.n_tombstones = h->last.n_del_survived;      // every DELETED survivor is a tombstone of the T-trace
+    if (use_part && (h->last.flags & (kFlagTableFull | kFlagPendingFull | kFlagSegmentsFull)) && !(h->last.flags & kFlagBadEvent)) {
+        // a partition's dictionary slice, the segment table or the pending list overflowed (hash imbalance, extreme
+        // skew): the sort path has no such limits
+        h->force_sort = true;
+        int rc2 = pte_run(h, flags, out);
+        h->force_sort = false;
+        return rc2;
+    }
+    h->last_path = use_part ? 1 : 0;
     int rc = check_flags(h, h->last.flags);
     if (rc) { h->carry_valid = false; return rc; }
     if (h->last.flags & kFlagUnordered) {
@@ -718,6 +862,13 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         out->n_passes = (u32)h->pass_ev_used;
         out->n_diff_rounds = h->n_diff_rounds;
         out->ms_pass_avg = h->pass_ev_used ? sum / h->pass_ev_used : 0.f;
+        out->path = (u32)h->last_path;
+        if (use_part) {
+            cudaEventElapsedTime(&out->ms_part_hist, h->ev[0], h->ev[6]);
+            cudaEventElapsedTime(&out->ms_part_scatter, h->ev[6], h->ev[1]);
+            cudaEventElapsedTime(&out->ms_part_replay, h->ev[7], h->ev[3]);
+            out->n_pending = h->last.n_pending;
+        }
     }
     return PTE_OK;
 }
@@ -737,8 +888,11 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
         if (key) {
             if (!h->key_valid) {
                 int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
-                key_lookup_kernel<<<grid, 256, 0, st>>>(h->out_idx, n, h->uid_hi, h->uid_lo, h->table,
-                                                        (u32)(h->table_cap - 1), h->out_key);
+                if (h->last_path == 1)
+                    key_lookup_part_kernel<<<grid, 256, 0, st>>>(h->out_idx, n, h->uid_hi, h->uid_lo, h->table, h->part_slice, h->out_key);
+                else
+                    key_lookup_kernel<<<grid, 256, 0, st>>>(h->out_idx, n, h->uid_hi, h->uid_lo, h->table,
+                                                            (u32)(h->table_cap - 1), h->out_key);
                 CK(h, cudaGetLastError());
                 h->key_valid = true;
             }

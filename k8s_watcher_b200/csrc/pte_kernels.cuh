@@ -28,10 +28,10 @@ struct Counters {
     u64 digest;
     u32 n_pods;
     u32 flags;
-    u32 ticket[4];         // tile tickets: [0] intern (filtered runs), [1] radix pass (reset per pass), [2..3] spare
+    u32 ticket[4];         // tile tickets: [0] spare, [1] radix pass (reset per pass), [2] partition scatter, [3] partition replay
     u32 sample_emit, sample_total;   // emit fraction of a sample of the sorted records
     u32 invert;            // 1: the diff stage clears the bits of suppressed records instead of setting emitted ones
-    u32 pad_;
+    u32 n_pending;         // partitioned runs: first events of a uid in a later segment, resolved by pending_fixup_kernel
 };
 
 __device__ __forceinline__ ulonglong2 cas128(Slot* addr, u64 cmp_hi, u64 cmp_lo, u64 val_hi, u64 val_lo) {

@@ -1,0 +1,650 @@
+// Partition-first replay: the T-trace of a large log without a global dictionary walk and without a sort.
+//
+// The per-event rule (it would sit at watcher/pod_watcher.py:236) only ever looks at
+// the PREVIOUS event of the same uid (metadata.uid, pod_watcher.py:164).  So the log is first split by a
+// hash of the uid into 1024 partitions, each keeping arrival order (one stable scatter of 24-byte records).
+// A partition holds 1/1024 of the pods: its slice of the uid dictionary is a few hundred KB and stays in
+// L2 while it is probed, and the last-known phase of all its pods fits in the shared memory of one CTA.
+// The CTA then simply replays the partition in order.
+//
+//   part_hist_kernel     uid hash -> partition counts (+ replay-order check)          16 B read / event
+//   part_scan_kernel     partition starts, segment table (long partitions are cut into segments)
+//   part_scatter_kernel  events -> 24-byte records (uid_hi, uid_lo, pos|type|phase), grouped by partition,
+//                        arrival order kept: warp-striped tile, ballot ranking, per-warp counts, tile
+//                        re-ordered in shared memory, runs written out; tiles chained by decoupled look-back
+//                                                                                     18 B read + 24 B written
+//   part_replay_kernel   one CTA per segment: tiles come in by 1-D bulk async copy (cp.async.bulk + mbarrier,
+//                        double-buffered), uids are interned in the partition's dictionary slice (L2 hits),
+//                        events are dealt to the warp that owns their slot (slot mod 16) keeping order, each
+//                        warp replays its queue 32 events at a time against the state bytes in shared
+//                        memory, emitted positions flip bits of the emit bitmap                24 B read
+//   pending_fixup_kernel first events of a uid inside a later segment of a cut partition: their
+//                        predecessor state is looked up in the state tables the earlier segments exported
+//
+// Skew (a pod that owns a few per cent of all events makes its partition many times the mean) is what the
+// segments are for: every segment replays independently from an "unknown" state, and only the first event
+// of each uid in a non-first segment needs the fix-up.
+#pragma once
+#include "pte_kernels.cuh"
+
+static constexpr int kPartBits = 10;
+static constexpr int kParts = 1 << kPartBits;
+static constexpr u64 kPartSalt = 0x7061727469746E21ull;
+static constexpr u32 kMinSegment = 1u << 15;          // records; shorter partitions are never cut
+static constexpr u32 kMaxSegments = 16 * kParts;
+static constexpr u32 kSampleSegments = 4;             // extra entries behind the segment table: the polarity sample
+
+__host__ __device__ __forceinline__ u32 part_of(u64 uid_lo) { return (u32)(mix64(uid_lo ^ kPartSalt) >> (64 - kPartBits)); }
+
+struct __align__(16) Segment {
+    u32 beg, end;          // records [beg, end) of the partition-ordered buffer
+    u32 part;              // partition
+    u32 ordinal;           // 0 for the first segment of its partition; bit 31: another segment follows
+};
+struct __align__(16) PendingHead {
+    u64 meta;              // pos << 8 | type << 6 | effective phase
+    u32 seg;               // global segment index (its partition's earlier segments are seg-1, seg-2, ...)
+    u32 slot;              // slot inside the partition's dictionary slice
+};
+
+enum : u32 { kFlagPendingFull = 8u, kFlagSegmentsFull = 16u };
+
+// state byte of a pod: 0 = no live phase known (never seen, or last event DELETED), 1 + phase, 0xFF = not seen in this segment
+__device__ __forceinline__ u32 state_after(u32 tp) { return (tp & 0x80u) ? 0u : 1u + (tp & 0x3Fu); }
+__device__ __forceinline__ bool emits(u32 pred_state, u32 tp) {
+    return (tp & 0x80u) || pred_state == 0u || pred_state - 1u != (tp & 0x3Fu);
+}
+
+// exclusive scan over all threads of a block of up to 1024 threads; `part` = 32 words of shared memory
+__device__ __forceinline__ u32 block_excl_scan(u32 v, u32* part, u32* total) {
+    const u32 lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    u32 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const u32 t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= (u32)o) inc += t; }
+    if (lane == 31) part[w] = inc;
+    __syncthreads();
+    u32 base = 0, all = 0;
+    for (u32 k = 0; k < nw; k++) { const u32 t = part[k]; if (k < w) base += t; all += t; }
+    if (total) *total = all;
+    __syncthreads();
+    return base + inc - v;
+}
+
+// ---- partition counts ---------------------------------------------------------------------------------
+struct PartHistArgs {
+    const u64* uid_lo; const u64* rv; const u32* keep;     // keep: FILTERED only (filter_flag_kernel's bitmap)
+    u64 n; u32* hist; Counters* ctr;
+};
+
+template <bool FILTERED>
+__global__ void __launch_bounds__(256) part_hist_kernel(PartHistArgs a) {
+    __shared__ u32 sh[kParts];
+    for (int k = threadIdx.x; k < kParts; k += 256) sh[k] = 0;
+    __syncthreads();
+    const u32 lane = threadIdx.x & 31;
+    u32 flags = 0;
+    const u64 n4 = (a.n + 3) / 4;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 wb = (u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); wb < n4; wb += stride) {
+        const u64 i0 = (wb + lane) * 4;
+        const ulonglong2* p = reinterpret_cast<const ulonglong2*>(a.uid_lo + i0);     // padded: readable past n
+        const ulonglong2 lx = __ldcs(p), ly = __ldcs(p + 1);
+        u32 keep_bits = 0xFu;
+        if (FILTERED) keep_bits = (a.keep[i0 >> 5] >> (i0 & 31)) & 0xFu;
+        else {
+            // replay order check: rv must not decrease along arrival order (filter_flag_kernel does it for FILTERED)
+            const ulonglong2* q = reinterpret_cast<const ulonglong2*>(a.rv + i0);
+            const ulonglong2 x = __ldcs(q), y = __ldcs(q + 1);
+            u64 prev = __shfl_up_sync(0xffffffffu, y.y, 1);
+            if (lane == 0) prev = i0 > 0 ? a.rv[i0 - 1] : 0;
+            if ((i0 < a.n && x.x < prev) || (i0 + 1 < a.n && x.y < x.x) || (i0 + 2 < a.n && y.x < x.y) ||
+                (i0 + 3 < a.n && y.y < y.x))
+                flags |= kFlagUnordered;
+        }
+        const u64 lo[4] = {lx.x, lx.y, ly.x, ly.y};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (i0 + k < a.n && ((keep_bits >> k) & 1u)) atomicAdd(&sh[part_of(lo[k])], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < kParts; k += 256)
+        if (sh[k]) atomicAdd(&a.hist[k], sh[k]);
+    flags = __reduce_or_sync(0xffffffffu, flags);
+    if (lane == 0 && flags) atomicOr(&a.ctr->flags, flags);
+}
+
+// ---- partition starts + segment table (one block of kParts threads) --------------------------------------
+// Segment length: seg_q8 / 256 of the mean partition size, never below kMinSegment.
+__global__ void __launch_bounds__(kParts)
+part_scan_kernel(const u32* __restrict__ hist, u32* __restrict__ part_start, Segment* __restrict__ segs, u32* __restrict__ n_segs,
+                 Counters* __restrict__ ctr, u32 seg_q8, int set_survived) {
+    __shared__ u32 s_part[32];
+    const u32 t = threadIdx.x;
+    const u32 c = hist[t];
+    u32 total;
+    const u32 ex = block_excl_scan(c, s_part, &total);
+    part_start[t] = ex;
+    if (t == 0) { part_start[kParts] = total; if (set_survived) ctr->n_survived = total; }
+    const u64 want = ((u64)total * seg_q8 + (u64)kParts * 256 - 1) / ((u64)kParts * 256);
+    const u32 seg_len = (u32)max((u64)kMinSegment, want);
+    const u32 ns = c ? (c + seg_len - 1) / seg_len : 0;
+    u32 stotal;
+    const u32 sb = block_excl_scan(ns, s_part, &stotal);
+    if (t == 0) {
+        n_segs[1] = kSampleSegments;
+        *n_segs = min(stotal, kMaxSegments);
+        if (stotal > kMaxSegments) atomicOr(&ctr->flags, kFlagSegmentsFull);
+    }
+    for (u32 j = 0; j < ns && sb + j < kMaxSegments; j++) {
+        Segment s;
+        s.beg = ex + j * seg_len;
+        s.end = min(ex + c, s.beg + seg_len);
+        s.part = t;
+        s.ordinal = j | (j + 1 < ns ? 0x80000000u : 0u);
+        segs[sb + j] = s;
+    }
+    // the polarity sample: a prefix of the first partitions, replayed without side effects on the bitmap
+    if (t < kSampleSegments) {
+        Segment s;
+        s.beg = ex; s.end = ex + min(c, 1u << 16); s.part = t; s.ordinal = 0;
+        segs[kMaxSegments + t] = s;
+    }
+}
+
+// ---- stable scatter of the events into partition order -------------------------------------------------------
+template <int THREADS, int ITEMS>
+struct ScatterCfg {
+    static constexpr int kWarps = THREADS / 32, kTile = THREADS * ITEMS, kWarpRecs = 32 * ITEMS;
+    static constexpr int kWords = kParts / 2;                 // u16 pairs: one word covers two partitions
+    static constexpr int kWordsPerThread = kWords / THREADS;  // words a thread owns in everything that is per partition
+    static_assert(kWords % THREADS == 0 && kWordsPerThread >= 1, "threads must divide kParts / 2");
+    static_assert(kTile % 16 == 0 && kTile / 16 <= THREADS, "phase/type bytes come in as one 16-byte load per thread");
+    static_assert(kWarpRecs * 1 < 65536 && kTile < 65536, "u16 counters");
+};
+
+template <int THREADS, int ITEMS>
+struct ScatterSmem {
+    using C = ScatterCfg<THREADS, ITEMS>;
+    u64 stage[C::kTile * 3];                 // the tile in partition order, 3 words per record
+    u32 whist[C::kWarps][C::kWords];         // per warp and partition: count, then start inside the tile's run (u16 pairs)
+    u32 tile_excl[kParts];                   // start of each partition's run inside the tile
+    u32 dst_off[kParts];                     // global record index of the run minus tile_excl
+    unsigned short sbin[C::kTile];           // partition of every staged record
+    u8 ph[C::kTile], ty[C::kTile];
+    u32 scan_part[32];
+    u32 tile, next_tile, survivors;
+};
+
+struct ScatterArgs {
+    const u64* uid_hi; const u64* uid_lo; const u8* phase; const u8* type; const u32* keep;
+    u64 n;
+    const u32* part_start;
+    u64* out;                                // 3 x u64 per survivor
+    u32* lookback; u32* ticket;
+    Counters* ctr;
+};
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS, bool FILTERED>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) part_scatter_kernel(ScatterArgs a) {
+    using C = ScatterCfg<THREADS, ITEMS>;
+    constexpr int kTile = C::kTile, kWarps = C::kWarps, kWarpRecs = C::kWarpRecs, WPT = C::kWordsPerThread;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ScatterSmem<THREADS, ITEMS>& s = *reinterpret_cast<ScatterSmem<THREADS, ITEMS>*>(smem_raw);
+    unsigned short* whist16 = reinterpret_cast<unsigned short*>(&s.whist[0][0]);
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 lt = lanemask_lt();
+    const u64 n = a.n;
+    // thread t owns the partitions of words t, t + THREADS, ... (two partitions per word)
+    u32 pbase[WPT][2];
+#pragma unroll
+    for (int j = 0; j < WPT; j++) {
+        const u32 w = tid + j * THREADS;
+        pbase[j][0] = a.part_start[2 * w]; pbase[j][1] = a.part_start[2 * w + 1];
+    }
+    u32 del_surv = 0, flags = 0;
+
+    if (tid == 0) s.tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    u32 tile = s.tile;
+
+    u64 hi[ITEMS], lo[ITEMS];
+    uint4 phv = make_uint4(0, 0, 0, 0), tyv = make_uint4(0, 0, 0, 0);
+    u32 keepw[FILTERED ? ITEMS : 1];
+    auto load_tile = [&](u32 t) {
+        const u64 base = (u64)t * kTile;
+        if (base >= n) return;
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            const u64 i = base + warp * kWarpRecs + k * 32 + lane;       // buffers are padded by more than a tile
+            lo[k] = __ldcs(a.uid_lo + i);
+            hi[k] = __ldcs(a.uid_hi + i);
+            if (FILTERED) keepw[k] = __ldg(a.keep + (i >> 5));             // one word per warp step
+        }
+        if (tid < kTile / 16) {
+            phv = __ldcs(reinterpret_cast<const uint4*>(a.phase + base) + tid);
+            tyv = __ldcs(reinterpret_cast<const uint4*>(a.type + base) + tid);
+        }
+    };
+    load_tile(tile);
+
+    for (;;) {
+        const u64 tile_base = (u64)tile * kTile;
+        if (tile_base >= n) break;
+        const u32 tile_valid = (u32)min((u64)kTile, n - tile_base);
+        // (1) phase/type bytes of the tile, per-warp counters cleared
+        if (tid < kTile / 16) {
+            reinterpret_cast<uint4*>(s.ph)[tid] = phv;
+            reinterpret_cast<uint4*>(s.ty)[tid] = tyv;
+        }
+        for (int k = tid; k < kWarps * C::kWords; k += THREADS) (&s.whist[0][0])[k] = 0;
+        if (tid == 0) s.next_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+
+        // (2) rank inside the warp, in arrival order: ballots over the partition bits give the lanes of the
+        // step that go to the same partition; the first of them advances the warp's counter for it
+        u32 bin[ITEMS];
+        unsigned short lrank[ITEMS];
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            const u32 j = warp * kWarpRecs + k * 32 + lane;
+            bool valid = j < tile_valid;
+            if (FILTERED) valid = valid && ((keepw[k] >> lane) & 1u);
+            const u32 b = part_of(lo[k]);
+            u32 peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+            for (int q = 0; q < kPartBits; q++) {
+                const bool bit = (b >> q) & 1u;
+                const u32 m = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? m : ~m;
+            }
+            if (!valid) peers = 0;
+            const u32 before = peers & lt;
+            u32 wbase = 0;
+            if (valid && before == 0) {
+                wbase = whist16[warp * kParts + b];
+                whist16[warp * kParts + b] = (unsigned short)(wbase + __popc(peers));
+            }
+            __syncwarp();
+            wbase = __shfl_sync(0xffffffffu, wbase, (__ffs(peers) - 1) & 31);
+            lrank[k] = (unsigned short)(wbase + __popc(before));
+            bin[k] = valid ? b : 0xFFFFFFFFu;
+        }
+        __syncthreads();
+
+        // (3) per partition: the tile's count (published at once), every warp's start inside the run
+        u32 cnt[WPT][2];
+        {
+            u32 sum = 0;
+#pragma unroll
+            for (int j = 0; j < WPT; j++) {
+                const u32 w = tid + j * THREADS;
+                u32 run = 0;
+#pragma unroll
+                for (int ww = 0; ww < kWarps; ww++) { const u32 v = s.whist[ww][w]; s.whist[ww][w] = run; run += v; }
+                cnt[j][0] = run & 0xFFFFu; cnt[j][1] = run >> 16;
+                u32* lb = a.lookback + (u64)tile * kParts + 2 * w;
+                const u32 fl = tile == 0 ? kLbInclusive : kLbPartial;
+                st_relaxed_u32(lb, fl | cnt[j][0]);
+                st_relaxed_u32(lb + 1, fl | cnt[j][1]);
+                sum += cnt[j][0] + cnt[j][1];
+            }
+            // partition order for the staging area: word-major over threads (thread t's words are t, t + THREADS, ...),
+            // any fixed order will do as long as (4) and (6) agree with it
+            u32 total;
+            u32 ex = block_excl_scan(sum, s.scan_part, &total);
+#pragma unroll
+            for (int j = 0; j < WPT; j++) {
+                const u32 w = tid + j * THREADS;
+                s.tile_excl[2 * w] = ex; ex += cnt[j][0];
+                s.tile_excl[2 * w + 1] = ex; ex += cnt[j][1];
+            }
+            if (tid == 0) s.survivors = total;
+        }
+        __syncthreads();
+        const u32 next_tile = s.next_tile;
+        const u32 survivors = s.survivors;
+
+        // (4) every record to its place in partition order
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            if (bin[k] != 0xFFFFFFFFu) {
+                const u32 j = warp * kWarpRecs + k * 32 + lane;
+                const u32 b = bin[k];
+                const u32 pos = s.tile_excl[b] + whist16[warp * kParts + b] + lrank[k];
+                const u32 ty = s.ty[j], ph = s.ph[j];
+                if (ty > kTypeDeleted || ph > kPhMax || (hi[k] | lo[k]) == 0) flags |= kFlagBadEvent;   // the run fails anyway
+                del_surv += ty == kTypeDeleted;
+                s.stage[pos * 3] = hi[k];
+                s.stage[pos * 3 + 1] = lo[k];
+                s.stage[pos * 3 + 2] = ((tile_base + j) << 8) | ((u64)(ty & 3u) << 6) | (eff_phase(ph) & 63u);
+                s.sbin[pos] = (unsigned short)b;
+            }
+        }
+        load_tile(next_tile);        // in flight during (5) and (6)
+
+        // (5) decoupled look-back for this thread's partitions
+#pragma unroll
+        for (int j = 0; j < WPT; j++) {
+            const u32 w = tid + j * THREADS;
+            u32 excl[2] = {0, 0};
+            if (tile > 0) {
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const u32* col = a.lookback + 2 * w + h;
+                    int t = (int)tile - 1;
+                    bool done = false;
+                    while (!done) {
+                        u32 v[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) v[q] = t - q >= 0 ? ld_relaxed_u32(col + (u64)(t - q) * kParts) : kLbInclusive;
+                        int used = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (done || (v[q] >> 30) == 0) break;
+                            excl[h] += v[q] & kLbValue;
+                            used++;
+                            if ((v[q] >> 30) == 2) done = true;
+                        }
+                        t -= used;
+                        if (!done && used == 0) __nanosleep(40);
+                    }
+                    st_relaxed_u32(a.lookback + (u64)tile * kParts + 2 * w + h, kLbInclusive | (excl[h] + cnt[j][h]));
+                }
+            }
+            s.dst_off[2 * w] = pbase[j][0] + excl[0] - s.tile_excl[2 * w];
+            s.dst_off[2 * w + 1] = pbase[j][1] + excl[1] - s.tile_excl[2 * w + 1];
+        }
+        __syncthreads();
+
+        // (6) runs out to global memory, word by word: a (tile, partition) run leaves as one contiguous piece
+#pragma unroll 4
+        for (u32 w = tid; w < survivors * 3; w += THREADS) {
+            const u32 rec = w / 3;
+            __stcs(a.out + (u64)(s.dst_off[s.sbin[rec]] + rec) * 3 + (w - rec * 3), s.stage[w]);
+        }
+        tile = next_tile;
+        __syncthreads();
+    }
+    del_surv = __reduce_add_sync(0xffffffffu, del_surv);
+    flags = __reduce_or_sync(0xffffffffu, flags);
+    if (lane == 0) {
+        if (del_surv) atomicAdd(&a.ctr->n_del_survived, (u64)del_surv);
+        if (flags) atomicOr(&a.ctr->flags, flags);
+    }
+}
+
+// ---- bulk async copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) ---------------------------------------------------
+__device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, u32 bytes, u64* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(dst)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(u64* bar, u32 parity) {
+    u32 done;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n" : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    return done != 0;
+}
+// Waiting warps must not eat the issue slots of the warps they wait for: back off between polls.
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity, u32 sleep_ns) {
+    while (!mbar_try_wait(bar, parity)) if (sleep_ns) __nanosleep(sleep_ns);
+}
+
+// ---- replay of the partitions ---------------------------------------------------------------------------
+// One CTA per segment, warp-specialised, tiles of 1024 records in a ring of three stages:
+//   * the tile's bytes arrive by one bulk async copy (cp.async.bulk, completion on an mbarrier);
+//   * fifteen PROBER warps intern the uids in the partition's dictionary slice (L2 hits; find-or-insert with the
+//     128-bit CAS) and leave every record's slot in shared memory, then arrive on the stage's second mbarrier;
+//   * one REPLAYER warp walks the tile in arrival order, 32 records per step, against the state bytes of the
+//     partition's pods in shared memory.  A step whose lanes all have different slots (the usual case, checked
+//     with a small mark table) is one load and one store per lane; otherwise MATCH.ANY gives the exact peers and
+//     the lanes of a slot chain their states in lane order.  After a tile the replayer refills the stage.
+// Order is kept by construction: one warp, one step after the other.  The probers run ahead of it, so the
+// latency of the dictionary never sits in that chain.
+static constexpr int kRpThreads = 512, kRpWarps = kRpThreads / 32, kRpTile = 1024;
+static constexpr int kRpProbers = kRpThreads - 32;    // threads of the prober warps
+static constexpr int kRpBufRecs = kRpTile + 2;        // a tile is copied from an even record index: 16-byte aligned
+static constexpr int kRpStages = 3;
+static constexpr int kRpMarks = 4096;
+
+struct ReplayArgs {
+    const u64* rec;                 // partition-ordered records, 3 words each
+    const Segment* segs; const u32* n_segs; u32* ticket;
+    u32 first_seg;                  // index of segs[0] in the global numbering (0; kMaxSegments for the sample)
+    Slot* table; u32 slice_slots;   // dictionary: kParts slices of slice_slots slots
+    u32* bitmap;
+    Counters* ctr;
+    u8* seg_export;                 // [segment][slice_slots] final state bytes of segments that are followed by another
+    PendingHead* pending; u32 pending_cap;
+    int count_only;
+};
+
+// dynamic shared memory: [kRpStages][kRpBufRecs*3] u64 | state[slice_slots] | the fixed part below
+struct ReplaySmemFixed {
+    unsigned short sslot[kRpStages][kRpTile];     // dictionary slot of every record of the tile
+    u8 mark[kRpMarks];                            // replayer: lane that last claimed a slot hash in the current step
+    u64 bar_tile[kRpStages];                      // bulk copy of the stage has landed
+    u64 bar_slots[kRpStages];                     // all prober warps are done with the stage
+    u32 seg;
+};
+
+struct ReplayCtx {
+    const ReplayArgs* a; u32 seg_id; bool invert;
+    u32 n_emit, n_seen;
+};
+// one event against the state `pred` of its pod
+__device__ __forceinline__ void replay_event(ReplayCtx& c, u32 pred, u64 meta, u32 slot) {
+    const u32 tp = (u32)meta & 0xFFu;
+    const ReplayArgs& a = *c.a;
+    if (pred == 0xFFu) {
+        // first event of this uid in a later segment: the predecessor lives in an earlier segment
+        if (!a.count_only) {
+            const u32 at = atomicAdd(&a.ctr->n_pending, 1u);
+            if (at < a.pending_cap) { PendingHead p; p.meta = meta; p.seg = c.seg_id; p.slot = slot; a.pending[at] = p; }
+            else atomicOr(&a.ctr->flags, kFlagPendingFull);
+        }
+    } else {
+        const bool e = emits(pred, tp);
+        c.n_emit += e; c.n_seen++;
+#ifndef PTE_EXP_NO_FLIP
+        if (!a.count_only && e != c.invert) flip_bit(a.bitmap, (u32)(meta >> 8));
+#endif
+    }
+}
+
+__device__ __forceinline__ void mbar_arrive(u64* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    u64* buf = reinterpret_cast<u64*>(smem_raw);
+    u8* state = smem_raw + kRpStages * kRpBufRecs * 24;
+    ReplaySmemFixed& f = *reinterpret_cast<ReplaySmemFixed*>(state + ((a.slice_slots + 15) & ~15u));
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 lt = lanemask_lt();
+    const u32 NS = a.slice_slots, smask = NS - 1;
+    const u64 pol = l2_policy_evict_last();
+    ReplayCtx cx;
+    cx.a = &a; cx.invert = a.ctr->invert != 0; cx.n_emit = 0; cx.n_seen = 0; cx.seg_id = 0;
+    u32 inserted = 0;
+    u32 par_tile = 0, par_slots = 0;         // phase parities, one bit per stage (every thread tracks the barriers it waits on)
+
+    if (tid == 0)
+        for (int b = 0; b < kRpStages; b++) { mbar_init(&f.bar_tile[b], 1); mbar_init(&f.bar_slots[b], kRpWarps - 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    const u32 n_segs = *a.n_segs;
+
+    for (;;) {
+        if (tid == 0) f.seg = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const u32 seg_local = f.seg;
+        if (seg_local >= n_segs) break;
+        const Segment sg = a.segs[seg_local];
+        cx.seg_id = a.first_seg + seg_local;
+        const bool later = (sg.ordinal & 0x7FFFFFFFu) != 0, has_next = (sg.ordinal >> 31) != 0;
+        const u32 n_rec = sg.end - sg.beg;
+        const u32 n_tiles = (n_rec + kRpTile - 1) / kRpTile;
+        Slot* slice = a.table + (u64)sg.part * NS;
+        // state bytes: "no live phase" for a first segment, "not seen here" otherwise
+        {
+            const u32 fill = later ? 0xFFFFFFFFu : 0u;
+            for (u32 k = tid; k < (NS + 3) / 4; k += kRpThreads) reinterpret_cast<u32*>(state)[k] = fill;
+        }
+        auto issue = [&](u32 t) {        // one thread: bulk copy of tile t into stage t % kRpStages
+            const u32 first = sg.beg + t * kRpTile, even = first & ~1u;
+            u64* bar = &f.bar_tile[t % kRpStages];
+            mbar_expect_tx(bar, kRpBufRecs * 24);
+            bulk_copy_g2s(buf + (t % kRpStages) * kRpBufRecs * 3, a.rec + (u64)even * 3, kRpBufRecs * 24, bar);
+        };
+        __syncthreads();                 // state initialised; everyone is done with the previous segment's stages
+        if (tid == 0) for (u32 t = 0; t < kRpStages && t < n_tiles; t++) issue(t);
+
+        if (warp != 0) {
+            // ---- probers: records -> dictionary slots
+            const u32 ptid = tid - 32;
+            for (u32 t = 0; t < n_tiles; t++) {
+                const u32 sidx = t % kRpStages;
+                const u32 first = sg.beg + t * kRpTile;
+                const u32 valid = min((u32)kRpTile, sg.end - first);
+                const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
+                mbar_wait(&f.bar_tile[sidx], (par_tile >> sidx) & 1u, 256);
+                par_tile ^= 1u << sidx;
+                // three records per thread at most (1024 = 2 * 480 + 64); all first probes in flight together
+                u32 r[3], sl[3];
+                u64 hi[3], lo[3];
+                ulonglong2 pv[3];
+                bool ok[3];
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    r[k] = ptid + k * kRpProbers;
+                    ok[k] = r[k] < valid;
+                    hi[k] = ok[k] ? tb[r[k] * 3] : 0; lo[k] = ok[k] ? tb[r[k] * 3 + 1] : 0;
+                    sl[k] = uid_home_slot(hi[k], lo[k], smask);
+                    pv[k] = make_ulonglong2(0, 0);
+                    if (ok[k]) pv[k] = ld_slot(slice + sl[k], pol);
+                }
+#pragma unroll
+                for (int k = 0; k < 3; k++)
+                    if (ok[k])
+#ifdef PTE_EXP_NO_PROBE
+                        f.sslot[sidx][r[k]] = (unsigned short)(sl[k] + (u32)(pv[k].x & 0));
+#else
+                        f.sslot[sidx][r[k]] = (unsigned short)intern_uid(slice, smask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
+#endif
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&f.bar_slots[sidx]);
+            }
+        } else {
+            // ---- replayer: the tile in arrival order, 32 records per step
+            for (u32 t = 0; t < n_tiles; t++) {
+                const u32 sidx = t % kRpStages;
+                const u32 first = sg.beg + t * kRpTile;
+                const u32 valid = min((u32)kRpTile, sg.end - first);
+                const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
+                mbar_wait(&f.bar_slots[sidx], (par_slots >> sidx) & 1u, 32);   // the probers waited for the tile's bytes
+                par_slots ^= 1u << sidx;
+                const unsigned short* ss = f.sslot[sidx];
+                u32 s_next = lane < valid ? (u32)ss[lane] : 0xFFFF0000u | lane;
+                u64 m_next = lane < valid ? tb[lane * 3 + 2] : 0;
+                for (u32 base = 0; base < valid; base += 32) {
+                    const u32 rr = base + lane;
+                    const bool active = rr < valid;
+                    const u32 s = s_next;
+                    const u64 meta = m_next;
+                    if (base + 32 < valid) {                                  // next step's operands, off the chain
+                        const u32 rn = rr + 32;
+                        s_next = rn < valid ? (u32)ss[rn] : 0xFFFF0000u | lane;
+                        m_next = rn < valid ? tb[rn * 3 + 2] : 0;
+                    }
+                    const u32 tp = (u32)meta & 0xFFu;
+                    const u32 h = s & (kRpMarks - 1);
+                    if (active) f.mark[h] = (u8)lane;
+                    __syncwarp();
+                    u32 pred = 0;
+                    bool clash = false;
+                    if (active) { clash = f.mark[h] != lane; pred = state[s]; }
+                    if (__any_sync(0xffffffffu, clash)) {
+                        // some lanes may share a slot: exact peers, states chained in lane order
+                        const u32 peers = __match_any_sync(0xffffffffu, s);
+                        const u32 lower = peers & lt;
+                        const u32 src = lower ? 31u - __clz(lower) : lane;
+                        const u32 ptp = __shfl_sync(0xffffffffu, tp, src);
+                        if (lower) pred = state_after(ptp);
+                        if (active && (peers >> lane) == 1u) state[s] = (u8)state_after(tp);      // last of its slot in this step
+                    } else if (active) {
+                        state[s] = (u8)state_after(tp);
+                    }
+                    if (active) replay_event(cx, pred, meta, s);
+                    __syncwarp();                                             // this step's state before the next step's loads
+                }
+                // the stage is free: probers and replayer are done with it
+                if (lane == 0 && t + kRpStages < n_tiles) issue(t + kRpStages);
+            }
+        }
+        __syncthreads();                 // the state bytes are final
+        if (has_next && !a.count_only) {
+            u32* dst = reinterpret_cast<u32*>(a.seg_export + (u64)cx.seg_id * NS);
+            for (u32 k = tid; k < NS / 4; k += kRpThreads) dst[k] = reinterpret_cast<const u32*>(state)[k];
+        }
+    }
+    inserted = __reduce_add_sync(0xffffffffu, inserted);
+    if (lane == 0 && inserted) atomicAdd(&a.ctr->n_pods, inserted);
+    if (a.count_only && warp == 0) {
+        const u32 n_emit = __reduce_add_sync(0xffffffffu, cx.n_emit);
+        const u32 n_seen = __reduce_add_sync(0xffffffffu, cx.n_seen);
+        if (lane == 0 && n_seen) { atomicAdd(&a.ctr->sample_emit, n_emit); atomicAdd(&a.ctr->sample_total, n_seen); }
+    }
+}
+
+// First events of a uid inside a later segment: find the state the nearest earlier segment of the same
+// partition left for that slot (0xFF = that segment never saw the uid), else "never seen".
+__global__ void __launch_bounds__(256)
+pending_fixup_kernel(const PendingHead* __restrict__ pending, u32 pending_cap, const Segment* __restrict__ segs,
+                     const u8* __restrict__ seg_export, u32 slice_slots, u32* __restrict__ bitmap, Counters* __restrict__ ctr) {
+    const u32 n = min(ctr->n_pending, pending_cap);
+    const bool invert = ctr->invert != 0;
+    for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const PendingHead p = pending[i];
+        const u32 ord = segs[p.seg].ordinal & 0x7FFFFFFFu;
+        u32 pred = 0;
+        for (u32 back = 1; back <= ord; back++) {
+            const u32 st = seg_export[(u64)(p.seg - back) * slice_slots + p.slot];
+            if (st != 0xFFu) { pred = st; break; }
+        }
+        if (emits(pred, (u32)p.meta & 0xFFu) != invert) flip_bit(bitmap, (u32)(p.meta >> 8));
+    }
+}
+
+// Interned key of each emitted record after a partitioned run: partition * slice_slots + slot.
+__global__ void __launch_bounds__(256)
+key_lookup_part_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict__ uid_hi, const u64* __restrict__ uid_lo,
+                       const Slot* __restrict__ table, u32 slice_slots, u64* __restrict__ out_key) {
+    const u32 smask = slice_slots - 1;
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
+        const u32 i = out_idx[j];
+        const u64 hi = uid_hi[i], lo = uid_lo[i];
+        const u32 part = part_of(lo);
+        const Slot* slice = table + (u64)part * slice_slots;
+        const u32 home = uid_home_slot(hi, lo, smask);
+        u64 key = ~0ull;
+        for (int p = 0; p < kMaxProbe; ++p) {
+            const u32 sl = probe_slot(home, p, smask);
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slice + sl);
+            if (v.x == hi && v.y == lo) { key = (u64)part * slice_slots + sl; break; }
+            if ((v.x | v.y) == 0) break;
+        }
+        out_key[j] = key;
+    }
+}

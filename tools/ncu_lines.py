@@ -7,7 +7,7 @@ rows = list(csv.reader(raw.splitlines()))
 starts = [i for i, r in enumerate(rows) if r and r[0] == 'File Path']
 blocks = [(starts[i], starts[i + 1] if i + 1 < len(starts) else len(rows)) for i in range(len(starts))]
 want = [b for b in blocks if rows[b[0]][1].endswith(src)]
-b = want[0]
+b = want[int(sys.argv[4]) if len(sys.argv) > 4 else 0]      # which captured launch of that kernel
 blk = rows[b[0]:b[1]]
 hdr = blk[2]
 ie = hdr.index('Instructions Executed'); ws = hdr.index('Warp Stall Sampling (All Samples)')
