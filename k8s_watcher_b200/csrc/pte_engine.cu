@@ -286,7 +286,7 @@ cudaError_t launch_scatter(pte_engine* h, int grid, bool filtered, const Scatter
 }
 
 int prepare_partition(pte_engine* h) {
-    h->replay_smem = kRpStages * kRpBufRecs * 24 + (int)((h->part_slice + 15) & ~15u) + (int)sizeof(ReplaySmemFixed);
+    h->replay_smem = kRpStages * kRpBufRecs * 24 + 2 * (int)((h->part_slice + 15) & ~15u) + (int)sizeof(ReplaySmemFixed);
     cudaError_t e = cudaErrorInvalidValue;
     switch (h->scatter_cfg) {
 #define X(id, T, I, B) case id: e = prepare_scatter<T, I, B>(h); break;
@@ -360,6 +360,18 @@ int run_partitioned(pte_engine* h, const InternArgs& a, bool filtered) {
     ra.segs = h->segs; ra.n_segs = h->part_nsegs; ra.first_seg = 0; ra.count_only = 0;
     part_replay_kernel<<<h->num_sms * h->replay_occ, kRpThreads, h->replay_smem, st>>>(ra);
     CK(h, cudaGetLastError());
+#ifdef PTE_EXP_TIMING
+    {
+        unsigned long long d[8];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(d, g_rp_dbg, sizeof(d));
+        const double k = 1.0 / 148.0 / 1.9e6;
+        fprintf(stderr, "replay timing per CTA (ms): prober0 wait-tile %.2f probe-issue %.2f resolve+deal %.2f barriers+queue %.2f | replayer1 wait %.2f steps %.2f\n",
+                d[0] * k, d[1] * k, d[2] * k, d[3] * k, d[4] * k, d[5] * k);
+        unsigned long long z[8] = {0};
+        cudaMemcpyToSymbol(g_rp_dbg, z, sizeof(z));
+    }
+#endif
     pending_fixup_kernel<<<h->num_sms * 4, 256, 0, st>>>(ra.pending, ra.pending_cap, h->segs, h->seg_export, NS, h->bitmap, h->ctr);
     CK(h, cudaGetLastError());
     h->n_launches += 6;

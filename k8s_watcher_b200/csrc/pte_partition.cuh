@@ -400,22 +400,86 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity, u32 sleep_ns) {
     while (!mbar_try_wait(bar, parity)) if (sleep_ns) __nanosleep(sleep_ns);
 }
 
+// ---- dictionary slice with fingerprint tags ---------------------------------------------------------------
+// Inside a partition the dictionary slice is used as lines of eight 16-byte slots (one 128-byte line).  A uid's
+// home line comes from its hash; it is stored in the first slot of the line (then of the following lines) that was
+// empty when it arrived, and slots never change once filled.  The CTA keeps one TAG byte per slot in shared
+// memory: 0 = not known to be filled, else an 8-bit fingerprint of the uid in the slot.  A lookup reads the
+// line's eight tags (one shared-memory load), loads only the slot whose tag matches and compares all 128 bits:
+// one L2 round trip per event instead of a probe run of dependent loads.  Tags are a cache, the slots are the
+// truth: a stale 0 tag (another CTA replaying a different segment of the same partition filled the slot) makes
+// the 128-bit CAS fail, which returns the slot's content and repairs the tag.
+struct UidHash { u32 line, fp; };
+__device__ __forceinline__ UidHash uid_hash(u64 hi, u64 lo, u32 line_mask) {
+    const u64 h = mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull));
+    UidHash r;
+    r.line = (u32)h & line_mask;
+    r.fp = (u32)(h >> 56);
+    r.fp += r.fp == 0;
+    return r;
+}
+__device__ __forceinline__ u64 bytes_equal(u64 t8, u32 b) {      // 0x80 in every byte of t8 equal to b (lowest hit exact, higher ones may be spurious)
+    const u64 rep = 0x0101010101010101ull;
+    const u64 x = t8 ^ (rep * b);
+    return (x - rep) & ~x & (rep << 7);
+}
+// full find-or-insert; `tags` is this CTA's tag array of the slice
+__device__ u32 intern_tagged(Slot* __restrict__ slice, u8* tags, u32 line_mask, u64 hi, u64 lo, u32& inserted,
+                             u32* __restrict__ flags, u64 pol) {
+    UidHash uh = uid_hash(hi, lo, line_mask);
+    u32 line = uh.line;
+    for (u32 walked = 0; walked <= line_mask;) {
+        const u64 t8 = *reinterpret_cast<volatile u64*>(tags + line * 8);
+        u64 m = bytes_equal(t8, uh.fp);
+        while (m) {
+            const u32 c = (u32)(__ffsll((long long)m) - 1) >> 3;
+            m &= m - 1;
+            const ulonglong2 v = ld_slot_cg(slice + line * 8 + c, pol);
+            if (v.x == hi && v.y == lo) return line * 8 + c;
+        }
+        const u64 e8 = bytes_equal(t8, 0);
+        if (e8) {
+            const u32 e = (u32)(__ffsll((long long)e8) - 1) >> 3;
+#ifdef PTE_EXP_NO_CAS
+            const ulonglong2 old = make_ulonglong2(0, 0);
+            slice[line * 8 + e].hi = hi; slice[line * 8 + e].lo = lo;
+#else
+            const ulonglong2 old = cas128(slice + line * 8 + e, 0, 0, hi, lo);
+#endif
+            if (old.x == 0 && old.y == 0) { tags[line * 8 + e] = (u8)uh.fp; inserted++; return line * 8 + e; }
+            tags[line * 8 + e] = (u8)uid_hash(old.x, old.y, line_mask).fp;       // filled by somebody else: repair the tag
+            if (old.x == hi && old.y == lo) return line * 8 + e;
+            continue;                                                            // same line again, with the new tag
+        }
+        line = (line + 1) & line_mask;
+        walked++;
+    }
+    atomicOr(flags, kFlagTableFull);
+    return 0;
+}
+
 // ---- replay of the partitions ---------------------------------------------------------------------------
-// One CTA per segment, warp-specialised, tiles of 1024 records in a ring of three stages:
+// One CTA of 1024 threads per segment, warp-specialised, tiles of 2048 records in a ring of three stages:
 //   * the tile's bytes arrive by one bulk async copy (cp.async.bulk, completion on an mbarrier);
-//   * fifteen PROBER warps intern the uids in the partition's dictionary slice (L2 hits; find-or-insert with the
-//     128-bit CAS) and leave every record's slot in shared memory, then arrive on the stage's second mbarrier;
-//   * one REPLAYER warp walks the tile in arrival order, 32 records per step, against the state bytes of the
-//     partition's pods in shared memory.  A step whose lanes all have different slots (the usual case, checked
-//     with a small mark table) is one load and one store per lane; otherwise MATCH.ANY gives the exact peers and
-//     the lanes of a slot chain their states in lane order.  After a tile the replayer refills the stage.
-// Order is kept by construction: one warp, one step after the other.  The probers run ahead of it, so the
-// latency of the dictionary never sits in that chain.
-static constexpr int kRpThreads = 512, kRpWarps = kRpThreads / 32, kRpTile = 1024;
-static constexpr int kRpProbers = kRpThreads - 32;    // threads of the prober warps
+//   * sixteen PROBER warps intern the uids in the partition's dictionary slice (L2 hits; find-or-insert with the
+//     128-bit CAS) and deal every record, keeping arrival order, to the replayer that owns its slot (slot mod 16):
+//     ballots over the four queue bits, per-warp counts, one scan over the 16 x 16 counts;
+//   * sixteen REPLAYER warps each walk their queue of the tile in order, 32 records per step, against the state
+//     bytes of their own pods in shared memory.  A step whose lanes all have different slots (the usual case,
+//     found with a mark byte per slot) is one load and one store per lane; otherwise MATCH.ANY gives the exact
+//     peers and the lanes of a slot chain their states in lane order.
+// A lone warp runs such a dependent step in 400+ cycles whatever the instruction count, which is why the tile's
+// pods are spread over sixteen of them; the probers run a stage or two ahead, so the dictionary's latency
+// never sits in a replayer's chain.  When all replayers are done with a stage, one of them refills it.
+static constexpr int kRpThreads = 1024, kRpWarps = kRpThreads / 32, kRpTile = 2048;
+static constexpr int kRpReplayers = 16, kRpProberWarps = kRpWarps - kRpReplayers, kRpProberThreads = kRpProberWarps * 32;
+static constexpr int kRpPerProber = kRpTile / kRpProberThreads;      // records per prober thread and tile
+static constexpr int kRpWarpRecs = kRpTile / kRpProberWarps;         // consecutive records one prober warp deals
+static constexpr int kRpQBits = 4;
 static constexpr int kRpBufRecs = kRpTile + 2;        // a tile is copied from an even record index: 16-byte aligned
 static constexpr int kRpStages = 3;
-static constexpr int kRpMarks = 4096;
+static constexpr int kRpMarks = 1024;                 // mark bytes per replayer
+static_assert(kRpReplayers == 1 << kRpQBits && kRpPerProber * kRpProberThreads == kRpTile, "replay geometry");
 
 struct ReplayArgs {
     const u64* rec;                 // partition-ordered records, 3 words each
@@ -429,12 +493,17 @@ struct ReplayArgs {
     int count_only;
 };
 
-// dynamic shared memory: [kRpStages][kRpBufRecs*3] u64 | state[slice_slots] | the fixed part below
+// dynamic shared memory: [kRpStages][kRpBufRecs*3] u64 | state[slice_slots] | tags[slice_slots] | the fixed part below
 struct ReplaySmemFixed {
     unsigned short sslot[kRpStages][kRpTile];     // dictionary slot of every record of the tile
-    u8 mark[kRpMarks];                            // replayer: lane that last claimed a slot hash in the current step
+    unsigned short queue[kRpStages][kRpTile];     // record indices grouped by replayer, arrival order inside a group
+    u32 qstart[kRpStages][kRpReplayers + 1];
+    u32 wcnt[kRpProberWarps][kRpReplayers];       // [dealing warp][queue]: count, then start
+    u8 mark[kRpReplayers][kRpMarks];              // per replayer: lane that last claimed a slot in the current step
+    u32 scan_tot[kRpReplayers];
     u64 bar_tile[kRpStages];                      // bulk copy of the stage has landed
     u64 bar_slots[kRpStages];                     // all prober warps are done with the stage
+    u64 bar_done[kRpStages];                      // all replayer warps are done with the stage
     u32 seg;
 };
 
@@ -465,23 +534,35 @@ __device__ __forceinline__ void replay_event(ReplayCtx& c, u32 pred, u64 meta, u
 __device__ __forceinline__ void mbar_arrive(u64* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
+__device__ __forceinline__ void prober_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kRpProberThreads) : "memory"); }
 
-__global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a) {
+#ifdef PTE_EXP_TIMING
+__device__ unsigned long long g_rp_dbg[8];
+#define RP_MARK(v) long long v = clock64();
+#define RP_ACC(i, from, cond) if ((cond) && lane == 0) atomicAdd(&g_rp_dbg[i], (unsigned long long)(clock64() - (from)));
+#else
+#define RP_MARK(v)
+#define RP_ACC(i, from, cond)
+#endif
+__global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
     u8* state = smem_raw + kRpStages * kRpBufRecs * 24;
-    ReplaySmemFixed& f = *reinterpret_cast<ReplaySmemFixed*>(state + ((a.slice_slots + 15) & ~15u));
+    u8* tags = state + ((a.slice_slots + 15) & ~15u);
+    ReplaySmemFixed& f = *reinterpret_cast<ReplaySmemFixed*>(tags + ((a.slice_slots + 15) & ~15u));
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 lt = lanemask_lt();
-    const u32 NS = a.slice_slots, smask = NS - 1;
+    const u32 NS = a.slice_slots, line_mask = NS / 8 - 1;
     const u64 pol = l2_policy_evict_last();
     ReplayCtx cx;
     cx.a = &a; cx.invert = a.ctr->invert != 0; cx.n_emit = 0; cx.n_seen = 0; cx.seg_id = 0;
     u32 inserted = 0;
-    u32 par_tile = 0, par_slots = 0;         // phase parities, one bit per stage (every thread tracks the barriers it waits on)
+    u32 par_a = 0, par_b = 0;      // phase parities, one bit per stage: probers (tile), replayers (slots, done)
 
     if (tid == 0)
-        for (int b = 0; b < kRpStages; b++) { mbar_init(&f.bar_tile[b], 1); mbar_init(&f.bar_slots[b], kRpWarps - 1); }
+        for (int b = 0; b < kRpStages; b++) {
+            mbar_init(&f.bar_tile[b], 1); mbar_init(&f.bar_slots[b], kRpProberWarps); mbar_init(&f.bar_done[b], kRpReplayers);
+        }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     const u32 n_segs = *a.n_segs;
@@ -500,7 +581,10 @@ __global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a
         // state bytes: "no live phase" for a first segment, "not seen here" otherwise
         {
             const u32 fill = later ? 0xFFFFFFFFu : 0u;
-            for (u32 k = tid; k < (NS + 3) / 4; k += kRpThreads) reinterpret_cast<u32*>(state)[k] = fill;
+            for (u32 k = tid; k < (NS + 3) / 4; k += kRpThreads) {
+                reinterpret_cast<u32*>(state)[k] = fill;
+                reinterpret_cast<u32*>(tags)[k] = 0;
+            }
         }
         auto issue = [&](u32 t) {        // one thread: bulk copy of tile t into stage t % kRpStages
             const u32 first = sg.beg + t * kRpTile, even = first & ~1u;
@@ -511,70 +595,142 @@ __global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a
         __syncthreads();                 // state initialised; everyone is done with the previous segment's stages
         if (tid == 0) for (u32 t = 0; t < kRpStages && t < n_tiles; t++) issue(t);
 
-        if (warp != 0) {
-            // ---- probers: records -> dictionary slots
-            const u32 ptid = tid - 32;
+        if (warp >= kRpReplayers) {
+            // ---- probers: records -> dictionary slots -> the owning replayer's queue
+            const u32 pw = warp - kRpReplayers, ptid = tid - kRpReplayers * 32;
             for (u32 t = 0; t < n_tiles; t++) {
                 const u32 sidx = t % kRpStages;
                 const u32 first = sg.beg + t * kRpTile;
                 const u32 valid = min((u32)kRpTile, sg.end - first);
                 const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
-                mbar_wait(&f.bar_tile[sidx], (par_tile >> sidx) & 1u, 256);
-                par_tile ^= 1u << sidx;
-                // three records per thread at most (1024 = 2 * 480 + 64); all first probes in flight together
-                u32 r[3], sl[3];
-                u64 hi[3], lo[3];
-                ulonglong2 pv[3];
-                bool ok[3];
+                if (lane < kRpReplayers) f.wcnt[pw][lane] = 0;
+                __syncwarp();
+                RP_MARK(t_a)
+                mbar_wait(&f.bar_tile[sidx], (par_a >> sidx) & 1u, 128);
+                par_a ^= 1u << sidx;
+                RP_ACC(0, t_a, pw == 0)
+                RP_MARK(t_b)
+                // this warp's records are consecutive; the tagged slot of every record is loaded before any is compared
+                u32 r[kRpPerProber], cand[kRpPerProber];
+                u64 hi[kRpPerProber], lo[kRpPerProber];
+                ulonglong2 pv[kRpPerProber];
+                bool ok[kRpPerProber];
 #pragma unroll
-                for (int k = 0; k < 3; k++) {
-                    r[k] = ptid + k * kRpProbers;
+                for (int k = 0; k < kRpPerProber; k++) {
+                    r[k] = pw * kRpWarpRecs + k * 32 + lane;
                     ok[k] = r[k] < valid;
                     hi[k] = ok[k] ? tb[r[k] * 3] : 0; lo[k] = ok[k] ? tb[r[k] * 3 + 1] : 0;
-                    sl[k] = uid_home_slot(hi[k], lo[k], smask);
+                    const UidHash uh = uid_hash(hi[k], lo[k], line_mask);
+                    const u64 m = ok[k] ? bytes_equal(*reinterpret_cast<volatile u64*>(tags + uh.line * 8), uh.fp) : 0ull;
+                    cand[k] = m ? uh.line * 8 + ((u32)(__ffsll((long long)m) - 1) >> 3) : 0xFFFFFFFFu;
                     pv[k] = make_ulonglong2(0, 0);
-                    if (ok[k]) pv[k] = ld_slot(slice + sl[k], pol);
-                }
-#pragma unroll
-                for (int k = 0; k < 3; k++)
-                    if (ok[k])
-#ifdef PTE_EXP_NO_PROBE
-                        f.sslot[sidx][r[k]] = (unsigned short)(sl[k] + (u32)(pv[k].x & 0));
+#ifndef PTE_EXP_NO_PROBE
+#if defined(PTE_EXP_NO_VERIFY)
+                    if (m) pv[k] = make_ulonglong2(hi[k], lo[k]);
+#elif defined(PTE_EXP_SAME_ADDR)
+                    if (m) { pv[k] = ld_slot_cg(slice + (cand[k] & 7u), pol); pv[k] = make_ulonglong2(hi[k] | (pv[k].x & 0), lo[k]); }
+#elif defined(PTE_EXP_L1)
+                    if (m) pv[k] = ld_slot(slice + cand[k], pol);
 #else
-                        f.sslot[sidx][r[k]] = (unsigned short)intern_uid(slice, smask, hi[k], lo[k], sl[k], pv[k], inserted, &a.ctr->flags, pol);
+                    if (m) pv[k] = ld_slot_cg(slice + cand[k], pol);
 #endif
+#endif
+                }
+                RP_ACC(1, t_b, pw == 0)
+                RP_MARK(t_c)
+                u32 q[kRpPerProber];
+                unsigned short lrank[kRpPerProber];
+#pragma unroll
+                for (int k = 0; k < kRpPerProber; k++) {
+                    u32 slot = 0;
+                    if (ok[k]) {
+                        if (cand[k] != 0xFFFFFFFFu && pv[k].x == hi[k] && pv[k].y == lo[k]) slot = cand[k];
+                        else slot = intern_tagged(slice, tags, line_mask, hi[k], lo[k], inserted, &a.ctr->flags, pol);
+                        f.sslot[sidx][r[k]] = (unsigned short)slot;
+                    }
+                    const u32 qq = slot & (kRpReplayers - 1);
+                    u32 peers = __ballot_sync(0xffffffffu, ok[k]);
+#pragma unroll
+                    for (int b = 0; b < kRpQBits; b++) {
+                        const bool bit = (qq >> b) & 1u;
+                        const u32 m = __ballot_sync(0xffffffffu, bit);
+                        peers &= bit ? m : ~m;
+                    }
+                    if (!ok[k]) peers = 0;
+                    const u32 before = peers & lt;
+                    u32 wb = 0;
+                    if (ok[k] && before == 0) { wb = f.wcnt[pw][qq]; f.wcnt[pw][qq] = wb + __popc(peers); }
+                    __syncwarp();
+                    wb = __shfl_sync(0xffffffffu, wb, (__ffs(peers) - 1) & 31);
+                    lrank[k] = (unsigned short)(wb + __popc(before));
+                    q[k] = qq;
+                }
+                RP_ACC(2, t_c, pw == 0)
+                RP_MARK(t_d)
+                prober_barrier();
+                // counts [dealing warp][queue] -> starts, queue-major: threads 0..255 hold one count each
+                u32 v = 0, incl = 0;
+                const u32 sq = ptid >> 4, sw = ptid & 15;
+                if (ptid < kRpProberWarps * kRpReplayers) {
+                    v = f.wcnt[sw][sq];
+                    incl = v;
+#pragma unroll
+                    for (int o = 1; o < 16; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, incl, o, 16); if ((lane & 15) >= (u32)o) incl += x; }
+                    if (sw == 15) f.scan_tot[sq] = incl;
+                }
+                prober_barrier();
+                if (ptid < kRpProberWarps * kRpReplayers) {
+                    u32 tot = lane < kRpReplayers ? f.scan_tot[lane] : 0u, ex = tot;
+#pragma unroll
+                    for (int o = 1; o < 16; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= (u32)o) ex += x; }
+                    ex -= tot;                                                // exclusive over the queues (lanes 0..15)
+                    const u32 qbase = __shfl_sync(0xffffffffu, ex, sq);
+                    f.wcnt[sw][sq] = qbase + incl - v;
+                    if (sw == 0) f.qstart[sidx][sq] = qbase;
+                    if (ptid == 0) f.qstart[sidx][kRpReplayers] = valid;
+                }
+                prober_barrier();
+#pragma unroll
+                for (int k = 0; k < kRpPerProber; k++)
+                    if (ok[k]) f.queue[sidx][f.wcnt[pw][q[k]] + lrank[k]] = (unsigned short)r[k];
                 __syncwarp();
+                RP_ACC(3, t_d, pw == 0)
                 if (lane == 0) mbar_arrive(&f.bar_slots[sidx]);
             }
         } else {
-            // ---- replayer: the tile in arrival order, 32 records per step
+            // ---- replayers: this warp's queue of the tile, in arrival order, 32 records per step
+            u8* mark = f.mark[warp];
             for (u32 t = 0; t < n_tiles; t++) {
                 const u32 sidx = t % kRpStages;
                 const u32 first = sg.beg + t * kRpTile;
-                const u32 valid = min((u32)kRpTile, sg.end - first);
                 const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
-                mbar_wait(&f.bar_slots[sidx], (par_slots >> sidx) & 1u, 32);   // the probers waited for the tile's bytes
-                par_slots ^= 1u << sidx;
+                RP_MARK(t_e)
+                mbar_wait(&f.bar_slots[sidx], (par_a >> sidx) & 1u, 32);      // the probers waited for the tile's bytes
+                par_a ^= 1u << sidx;
+                RP_ACC(4, t_e, warp == 1)
+                RP_MARK(t_f)
                 const unsigned short* ss = f.sslot[sidx];
-                u32 s_next = lane < valid ? (u32)ss[lane] : 0xFFFF0000u | lane;
-                u64 m_next = lane < valid ? tb[lane * 3 + 2] : 0;
-                for (u32 base = 0; base < valid; base += 32) {
-                    const u32 rr = base + lane;
-                    const bool active = rr < valid;
+                const unsigned short* qu = f.queue[sidx];
+                const u32 qb = f.qstart[sidx][warp], qe = f.qstart[sidx][warp + 1];
+                u32 s_next = 0xFFFF0000u | lane;
+                u64 m_next = 0;
+                if (qb + lane < qe) { const u32 rec = qu[qb + lane]; s_next = ss[rec]; m_next = tb[rec * 3 + 2]; }
+                for (u32 base = qb; base < qe; base += 32) {
+                    const bool active = base + lane < qe;
                     const u32 s = s_next;
                     const u64 meta = m_next;
-                    if (base + 32 < valid) {                                  // next step's operands, off the chain
-                        const u32 rn = rr + 32;
-                        s_next = rn < valid ? (u32)ss[rn] : 0xFFFF0000u | lane;
-                        m_next = rn < valid ? tb[rn * 3 + 2] : 0;
+                    if (base + 32 < qe) {                                     // next step's operands, off the chain
+                        const u32 in = base + 32 + lane;
+                        s_next = 0xFFFF0000u | lane; m_next = 0;
+                        if (in < qe) { const u32 rec = qu[in]; s_next = ss[rec]; m_next = tb[rec * 3 + 2]; }
                     }
                     const u32 tp = (u32)meta & 0xFFu;
-                    const u32 h = s & (kRpMarks - 1);
-                    if (active) f.mark[h] = (u8)lane;
+                    const u32 h = (s >> kRpQBits) & (kRpMarks - 1);
+                    if (active) mark[h] = (u8)lane;
                     __syncwarp();
                     u32 pred = 0;
                     bool clash = false;
-                    if (active) { clash = f.mark[h] != lane; pred = state[s]; }
+                    if (active) { clash = mark[h] != lane; pred = state[s]; }
                     if (__any_sync(0xffffffffu, clash)) {
                         // some lanes may share a slot: exact peers, states chained in lane order
                         const u32 peers = __match_any_sync(0xffffffffu, s);
@@ -589,8 +745,14 @@ __global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a
                     if (active) replay_event(cx, pred, meta, s);
                     __syncwarp();                                             // this step's state before the next step's loads
                 }
-                // the stage is free: probers and replayer are done with it
-                if (lane == 0 && t + kRpStages < n_tiles) issue(t + kRpStages);
+                RP_ACC(5, t_f, warp == 1)
+                if (lane == 0) mbar_arrive(&f.bar_done[sidx]);
+                if (warp == 0 && t + kRpStages < n_tiles) {
+                    // the stage is free once every replayer is done with it: refill
+                    mbar_wait(&f.bar_done[sidx], (par_b >> sidx) & 1u, 32);
+                    if (lane == 0) issue(t + kRpStages);
+                }
+                if (warp == 0) par_b ^= 1u << sidx;
             }
         }
         __syncthreads();                 // the state bytes are final
@@ -601,7 +763,7 @@ __global__ void __launch_bounds__(kRpThreads, 2) part_replay_kernel(ReplayArgs a
     }
     inserted = __reduce_add_sync(0xffffffffu, inserted);
     if (lane == 0 && inserted) atomicAdd(&a.ctr->n_pods, inserted);
-    if (a.count_only && warp == 0) {
+    if (a.count_only && warp < kRpReplayers) {
         const u32 n_emit = __reduce_add_sync(0xffffffffu, cx.n_emit);
         const u32 n_seen = __reduce_add_sync(0xffffffffu, cx.n_seen);
         if (lane == 0 && n_seen) { atomicAdd(&a.ctr->sample_emit, n_emit); atomicAdd(&a.ctr->sample_total, n_seen); }
@@ -631,19 +793,19 @@ pending_fixup_kernel(const PendingHead* __restrict__ pending, u32 pending_cap, c
 __global__ void __launch_bounds__(256)
 key_lookup_part_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict__ uid_hi, const u64* __restrict__ uid_lo,
                        const Slot* __restrict__ table, u32 slice_slots, u64* __restrict__ out_key) {
-    const u32 smask = slice_slots - 1;
+    const u32 line_mask = slice_slots / 8 - 1;
     for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
         const u32 i = out_idx[j];
         const u64 hi = uid_hi[i], lo = uid_lo[i];
         const u32 part = part_of(lo);
         const Slot* slice = table + (u64)part * slice_slots;
-        const u32 home = uid_home_slot(hi, lo, smask);
+        u32 sl = uid_hash(hi, lo, line_mask).line * 8;
         u64 key = ~0ull;
-        for (int p = 0; p < kMaxProbe; ++p) {
-            const u32 sl = probe_slot(home, p, smask);
+        for (u32 p = 0; p < slice_slots; ++p) {           // slots in probe order: the uid sits before the first empty one
             const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slice + sl);
             if (v.x == hi && v.y == lo) { key = (u64)part * slice_slots + sl; break; }
             if ((v.x | v.y) == 0) break;
+            sl = (sl + 1) & (slice_slots - 1);
         }
         out_key[j] = key;
     }

@@ -13,6 +13,13 @@ re-raise, ``watch.stop()`` always).  What changes is where the work happens:
   ``dedupe=False`` reproduces the reference literally: every event that reaches the POST site.
 * emitted records come back as a :class:`Batch`; the sink takes it in one call.
 
+DEVIATION FROM THE REFERENCE, on purpose: the default is ``dedupe=True`` (transition notifications only).
+The reference as shipped would notify on EVERY event that passes its filters; construct the watcher
+with ``dedupe=False`` to get exactly that.  The live loop flushes every ``flush_every`` events
+(default 4096) or ``flush_interval`` seconds (default 1.0), whichever comes first, and on every exit path.
+Events are ordered by ARRIVAL, like the reference's ``for event in stream`` loop: the live loop numbers
+them itself and never looks at ``metadata.resource_version`` (the reference does not read it either).
+
 There is no CPU implementation of the path in this package: without libpte.so and a CUDA
 device ``replay``/``flush`` raise.
 """
@@ -20,16 +27,20 @@ from __future__ import annotations
 
 import logging
 import os
+import time
 from datetime import datetime
 from typing import Any, Dict, Iterator, List, Optional
 
 import yaml
 
-try:                                     # a real kubernetes install wins
+try:
     from kubernetes import client, config, watch
     from kubernetes.config import ConfigException
-except ImportError:                      # this image: no package, no network
-    from ._k8s_stub import client, config, watch, ConfigException
+except ImportError:                      # no kubernetes package: replay() still works, the live loop reports the set-up failure
+    client = config = watch = None
+
+    class ConfigException(Exception):
+        pass
 
 from . import codes
 from .clusterapi_client import ClusterApiClient
@@ -119,13 +130,13 @@ def payload_fragments(watcher: "PodWatcher", log: ReplayLog, event_timestamp: st
 class PodWatcher:
     def __init__(self, environment: str = "development", *, dedupe: bool = True,
                  sink: Optional[ClusterApiClient] = None, engine: Optional[PhaseTransitionEngine] = None,
-                 device: int = 0, config_dir: str = "config", flush_every: Optional[int] = None,
-                 max_pods: int = 1 << 20, keep_batches: Optional[int] = None):
+                 device: int = 0, config_dir: str = "config", flush_every: Optional[int] = 4096,
+                 flush_interval: Optional[float] = 1.0, max_pods: int = 1 << 20, keep_batches: Optional[int] = 4):
         self.environment = environment
         self.config_dir = config_dir           # CWD-relative by default, like upstream (:22,:25)
         self.config = self._load_environment_config()
         self.v1 = None
-        self.watch = watch.Watch()
+        self.watch = watch.Watch() if watch is not None else None
         self._setup_logging()
         self.dedupe = dedupe
         self.clusterapi_client = sink          # the reference leaves this commented out (:14)
@@ -139,6 +150,9 @@ class PodWatcher:
         # live loop: replay every `flush_every` queued events as one batch of a stream; the engine carries the
         # uid dictionary and each pod's last known phase from batch to batch (None: one replay at stream end)
         self.flush_every = flush_every
+        self.flush_interval = flush_interval
+        self._last_flush = time.monotonic()
+        self._seq = 0                                # arrival number of the next live event (the stream's order key)
         self.max_pods = max_pods
         self._stream_namespaces: List[str] = []      # namespace dictionary shared by all batches of a stream
 
@@ -200,6 +214,9 @@ class PodWatcher:
 
     # ---- kubernetes client (pod_watcher.py:110-157) -----------------------------
     def setup_k8s_client(self) -> bool:
+        if client is None:
+            self.logger.error("Error setting up k8s client: the kubernetes package is not installed")
+            return False
         try:
             k8s = self.config.get("kubernetes", {})
             if k8s.get("use_incluster_config", False):
@@ -269,8 +286,11 @@ class PodWatcher:
 
     def handle_pod_event(self, event_type: str, pod) -> None:
         """Queue one event for the next bulk replay (the reference decides per event, :214-241)."""
+        md = getattr(pod, "metadata", None)
+        self.logger.info("Pod event detected: %s - %s/%s", event_type, getattr(md, "namespace", None), getattr(md, "name", None))
         self._pending.append({"type": event_type, "object": pod})
-        if self.flush_every and len(self._pending) >= self.flush_every:
+        due = self.flush_interval is not None and time.monotonic() - self._last_flush >= self.flush_interval
+        if (self.flush_every and len(self._pending) >= self.flush_every) or due:
             self.flush()
 
     # ---- bulk path -----------------------------------------------------------------
