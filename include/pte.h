@@ -83,6 +83,8 @@ typedef struct pte_stats {
     float ms_part_hist;     /* path 1: uid hash -> partition counts + replay-order check + segment table */
     float ms_part_scatter;  /* path 1: stable scatter of the events into 24-byte partition records */
     float ms_part_replay;   /* path 1: in-order replay of every partition against shared-memory state (+ fix-up) */
+    uint32_t n_rebuilds;    /* PTE_RUN_CARRY streams: times the dictionary was rebuilt from its live pods so far */
+    float ms_rebuild;       /* device time of the last such rebuild */
 } pte_stats;
 
 /* Parameters of the synthetic replay log (see "Synthetic replay logs" below). */
@@ -124,7 +126,9 @@ int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_
 /* ---- input -------------------------------------------------------------- */
 
 /* Copy a log of n events from host columns to the device (replaces the current log).
- * Stands in for the `for event in stream` producer, pod_watcher.py:264-268. */
+ * Stands in for the `for event in stream` producer, pod_watcher.py:264-268.
+ * ns_id may be NULL while no namespace allow-list is set (nothing on the path reads it then,
+ * pod_watcher.py:226-229 is a no-op; the ns_id output column reads 0): saves 4 of the 30 bytes per event. */
 int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
                const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n);
 
@@ -177,6 +181,18 @@ int pte_run(pte_handle h, int flags, pte_stats* out);
 int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t* ns_id,
               uint8_t* phase, uint8_t* type, uint64_t cap, uint64_t* n_out);
 
+/* The same result as one bit per event: bit (i & 31) of words[i >> 5] is set iff event i of the resident log
+ * reaches the notification site pod_watcher.py:232-236 (and, with dedupe, is a transition).  A host that still
+ * holds the log needs nothing else for the payload hand-off, and downloads 1 bit per event instead of the
+ * 5 bytes per notification of pte_fetch(idx, type).  words: (n_events + 31) / 32 uint32 (NULL: only *n_emitted).
+ * Not available (PTE_ERR_STATE) when the run had to pre-sort the log by rv: use pte_fetch then. */
+int pte_fetch_bitmap(pte_handle h, uint32_t* words, uint64_t cap_words, uint64_t* n_emitted);
+
+/* Raise max_events of a live engine without touching the uid dictionary or the per-pod state a PTE_RUN_CARRY
+ * stream carries: the live loop (pod_watcher.py:264-269) may meet a longer batch than any before.  The resident
+ * log and the results of the last run are dropped; ingest again.  No-op when max_events is not larger. */
+int pte_grow(pte_handle h, uint64_t max_events);
+
 /* The request bodies the reference would POST for emitted records [first, first + count) of the last pte_run:
  * json.dumps(_extract_pod_data(pod) + event_type) (pod_watcher.py:159-202, :233; clusterapi_client.py:36),
  * for pods that carry only what a replay-log row holds (name "pod-" + uid[:13], no labels, containers, ...).
@@ -214,8 +230,9 @@ int pte_debug_sort_u64(pte_handle h, uint64_t* records, uint64_t n, int bit_lo, 
  * out receives the n records of `in` stably partitioned by the digit in bits [bit_lo, bit_lo + n_bits)
  * (n_bits 1..8) -- the same result as pte_debug_sort_u64 on that bit range.  in and out are distinct,
  * caller-owned, 8-byte aligned and reachable from the GPU (device memory, or pinned host memory such as
- * pte_host_alloc returns); no padding is needed.  The work runs on `stream` (a cudaStream_t, NULL for
- * the default stream) of the current device and the call returns when it is done.
+ * pte_host_alloc returns); no padding is needed.  The work runs on `stream` (a cudaStream_t; NULL is the
+ * legacy default stream) of the current device; the call waits for that stream (cudaStreamSynchronize)
+ * before it returns, so the result is in `out` when it does.
  * The histogram and look-back scratch is a fixed array inside the library's device image, about 1 MB that
  * every GPU which loads libpte.so holds until the process exits.  Hence:
  *   - n may not exceed PTE_STATIC_MAX_RECORDS; more is refused with PTE_ERR_CAPACITY;

@@ -30,6 +30,7 @@ class PteStats(C.Structure):
         ("ms_sort_order", C.c_float), ("ms_assemble", C.c_float), ("ms_pass_avg", C.c_float),
         ("n_passes", C.c_uint32), ("n_diff_rounds", C.c_uint32), ("path", C.c_uint32), ("n_pending", C.c_uint32),
         ("ms_part_hist", C.c_float), ("ms_part_scatter", C.c_float), ("ms_part_replay", C.c_float),
+        ("n_rebuilds", C.c_uint32), ("ms_rebuild", C.c_float),
     ]
 
     def as_dict(self):
@@ -61,6 +62,8 @@ SYMBOLS = {
     "pte_read_log": (C.c_int, [C.c_void_p, _u64p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, _u64p]),
     "pte_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PteStats)]),
     "pte_fetch": (C.c_int, [C.c_void_p, _u32p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, _u64p]),
+    "pte_fetch_bitmap": (C.c_int, [C.c_void_p, _u32p, C.c_uint64, _u64p]),
+    "pte_grow": (C.c_int, [C.c_void_p, C.c_uint64]),
     "pte_digest": (C.c_int, [C.c_void_p, _u64p]),
     "pte_serialize_payloads": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint32, _u32p, C.c_uint32,
                                          C.c_uint32, C.c_void_p, C.c_uint64, _u64p, _u64p]),

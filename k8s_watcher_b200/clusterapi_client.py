@@ -1,10 +1,9 @@
 """Sink side of the watcher: same surface as the reference's ClusterApiClient
 (watcher/clusterapi_client.py:6-61), plus a batched call for the bulk engine.
 
-There is no network where this runs, so the default transport is an in-memory
-mock that records every request body and answers 200.  ``transport`` may be any
-callable ``(method, url, body_bytes_or_None, headers, timeout) -> status_code``;
-:func:`requests_transport` gives the reference's real behaviour.
+The default transport is ``requests.Session`` like the reference's (:func:`requests_transport`).
+``transport`` may be any callable ``(method, url, body_bytes_or_None, headers, timeout) -> status_code``;
+the tests inject a recording one (tests/mock_transport.py), since there is no network where they run.
 """
 from __future__ import annotations
 
@@ -19,21 +18,6 @@ class ConnectionFailed(Exception):
 
 class RequestTimeout(Exception):
     """Raised by a transport whose request timed out."""
-
-
-class MockTransport:
-    """Records what would have gone on the wire."""
-
-    def __init__(self, status: int = 200):
-        self.status = status
-        self.requests: List[Dict[str, Any]] = []
-
-    def __call__(self, method, url, body, headers, timeout):
-        self.requests.append({"method": method, "url": url, "body": body, "headers": dict(headers)})
-        return self.status
-
-    def bodies(self) -> List[bytes]:
-        return [r["body"] for r in self.requests if r["method"] == "POST"]
 
 
 def requests_transport():
@@ -72,12 +56,13 @@ class ClusterApiClient:
         self.delay_seconds = float(delay_seconds)
         import time as _time
         self._sleep = sleep if sleep is not None else _time.sleep
-        self.transport = transport if transport is not None else MockTransport()
+        self.transport = transport if transport is not None else requests_transport()
         self.session = self.transport            # the reference exposes .session; keep the name alive
         self.logger = logging.getLogger(__name__)
-        self.headers: Dict[str, str] = {}
-        if self.api_key:                          # clusterapi_client.py:14-18
-            self.headers = {"Authorization": "Bearer %s" % self.api_key, "Content-Type": "application/json"}
+        # session.post(json=...) always sends this header (clusterapi_client.py:36); the bearer token only with a key (:14-18)
+        self.headers: Dict[str, str] = {"Content-Type": "application/json"}
+        if self.api_key:
+            self.headers["Authorization"] = "Bearer %s" % self.api_key
 
     @classmethod
     def from_config(cls, config: Dict[str, Any], **kw) -> "ClusterApiClient":

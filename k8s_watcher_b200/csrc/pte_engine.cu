@@ -84,6 +84,8 @@ struct pte_engine {
     u64 n_events = 0;
     // interning dictionary
     Slot* table = nullptr;
+    Slot* table_spare = nullptr;                             // target of the next stream-dictionary rebuild (allocated on first use)
+    u32 n_rebuilds = 0; float ms_last_rebuild = 0.f;
     u64 table_cap = 0;
     RecLayout L{};
     // sort
@@ -132,13 +134,15 @@ struct pte_engine {
     Counters* ctr = nullptr;
     // filters
     u32* ns_bitmap = nullptr;
-    u32 ns_words = 0;
+    u32 ns_words = 0, ns_bitmap_cap = 0;
+    std::vector<u32> ns_bitmap_host;
     int ns_filter_on = 0, critical_only = 0;
     // outputs
     u32 *out_idx = nullptr, *out_ns = nullptr;
     u64 *out_rv = nullptr, *out_key = nullptr;
     u8 *out_phase = nullptr, *out_type = nullptr;
     bool has_run = false;
+    bool ns_loaded = true;                                   // the ns column holds caller data (or generator output), not zeros
     Counters last{};
     // timing
     std::vector<cudaEvent_t> ev;
@@ -285,6 +289,32 @@ cudaError_t launch_scatter(pte_engine* h, int grid, bool filtered, const Scatter
     return cudaGetLastError();
 }
 
+// Everything whose size follows max_events (log columns, record buffers, bitmaps, look-back words, output columns).
+// Used by pte_create and by pte_grow; the dictionary and the per-pod state are not touched.
+int alloc_event_buffers(pte_engine* h) {
+    h->cap_ev = round_up(h->max_events, kPad) + kPad;
+    const u64 c = h->cap_ev;
+    int rc = 0;
+    rc |= dev_alloc(h, &h->uid_hi, c); rc |= dev_alloc(h, &h->uid_lo, c); rc |= dev_alloc(h, &h->rv, c);
+    rc |= dev_alloc(h, &h->ns, c); rc |= dev_alloc(h, &h->phase, c); rc |= dev_alloc(h, &h->type, c);
+    rc |= dev_alloc(h, &h->rec_pool, 3 * c);
+    rc |= dev_alloc(h, &h->bitmap, c / 32); rc |= dev_alloc(h, &h->keepmap, c / 32);
+    // look-back words: one per (radix tile, digit); one per (partition-scatter tile, partition)
+    const u64 min_tile = 2048;
+    h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
+    h->lookback_words = std::max<u64>(h->lookback_words, (c / 2048 + 1) * kParts);
+    rc |= dev_alloc(h, &h->lookback, h->lookback_words);
+    rc |= dev_alloc(h, &h->out_idx, c); rc |= dev_alloc(h, &h->out_ns, c);
+    rc |= dev_alloc(h, &h->out_rv, c); rc |= dev_alloc(h, &h->out_key, c);
+    rc |= dev_alloc(h, &h->out_phase, c); rc |= dev_alloc(h, &h->out_type, c);
+    if (rc) return PTE_ERR_CUDA;
+    h->recA = h->rec_pool; h->recB = h->rec_pool + c; h->recC = h->rec_pool + 2 * c;
+    // pads must be readable garbage-free for the vector loads past n
+    CK(h, cudaMemsetAsync(h->rv, 0, c * sizeof(u64), h->stream));
+    CK(h, cudaMemsetAsync(h->ns, 0, c * sizeof(u32), h->stream));
+    return PTE_OK;
+}
+
 int prepare_partition(pte_engine* h) {
     h->replay_smem = kRpStages * kRpBufRecs * 24 + 2 * (int)((h->part_slice + 15) & ~15u) + (int)sizeof(ReplaySmemFixed);
     cudaError_t e = cudaErrorInvalidValue;
@@ -378,6 +408,34 @@ int run_partitioned(pte_engine* h, const InternArgs& a, bool filtered) {
     return PTE_OK;
 }
 
+// Stream dictionary full (or nearly): keep the pods with a live phase, forget the rest.  Returns the live count.
+int rebuild_stream_table(pte_engine* h) {
+    cudaStream_t st = h->stream;
+    if (!h->table_spare) CK(h, cudaMalloc((void**)&h->table_spare, h->table_alloc * sizeof(Slot)));
+    cudaEvent_t e0, e1;
+    CK(h, cudaEventCreate(&e0)); CK(h, cudaEventCreate(&e1));
+    CK(h, cudaEventRecord(e0, st));
+    CK(h, cudaMemsetAsync(h->table_spare, 0, h->table_cap * sizeof(Slot), st));
+    CK(h, cudaMemsetAsync(h->state_new, 0, h->table_cap, st));
+    CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
+    const int grid = (int)std::min<u64>((h->table_cap + 255) / 256, (u64)h->num_sms * 16);
+    rebuild_table_kernel<<<grid, 256, 0, st>>>(h->table, h->state_old, h->table_cap, h->table_spare, h->state_new,
+                                               (u32)(h->table_cap - 1), h->ctr);
+    CK(h, cudaGetLastError());
+    Counters c;
+    CK(h, cudaMemcpyAsync(&c, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaEventRecord(e1, st));
+    CK(h, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&h->ms_last_rebuild, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (c.flags & kFlagTableFull) FAIL(h, PTE_ERR_TABLE_FULL, "more pods alive at once than the engine was created for (max_pods)");
+    std::swap(h->table, h->table_spare);
+    std::swap(h->state_old, h->state_new);
+    h->pods_total = c.n_pods;
+    h->n_rebuilds++;
+    return PTE_OK;
+}
+
 // Bring a log whose rv decreases somewhere into replay order (ascending rv, ties by arrival) in shadow
 // columns, run the pipeline on those, map the emitted indices back to arrival indices.
 int run_reordered(pte_engine* h, int flags, pte_stats* out) {
@@ -448,7 +506,7 @@ void pte_destroy(pte_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->rec_pool, h->part_hist, h->part_start, h->part_nsegs, h->segs, h->seg_export, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->table, h->table_spare, h->rec_pool, h->part_hist, h->part_start, h->part_nsegs, h->segs, h->seg_export, h->bitmap, h->keepmap, h->state_old, h->state_new, h->lookback,
                     h->hist, h->ctr, h->ns_bitmap, h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase,
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
                     h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
@@ -470,7 +528,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     if (max_events == 0) max_events = 1;
     if (max_events > kMaxEvents)
         FAIL((pte_handle) nullptr, PTE_ERR_CAPACITY, "max_events above 2^30-1 per engine: shard the log by uid");
-    if (max_pods == 0 || max_pods > max_events) max_pods = max_events;
+    if (max_pods == 0) max_pods = max_events;      // the dictionary is sized by max_pods alone: a stream of short batches may know many pods
 
     pte_engine* h = new pte_engine();
     h->device = device; h->max_events = max_events; h->max_pods = max_pods;
@@ -515,35 +573,19 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKCU(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     CKCU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(prepare_pass_cfg(h));
-    h->cap_ev = round_up(max_events, kPad) + kPad;
-    const u64 c = h->cap_ev;
-    CKC(dev_alloc(h, &h->uid_hi, c)); CKC(dev_alloc(h, &h->uid_lo, c)); CKC(dev_alloc(h, &h->rv, c));
-    CKC(dev_alloc(h, &h->ns, c)); CKC(dev_alloc(h, &h->phase, c)); CKC(dev_alloc(h, &h->type, c));
     // the partition-first path views the dictionary as kParts slices of part_slice slots (at least 256 each)
     h->part_slice = (u32)std::max<u64>(256, h->table_cap / kParts);
     h->table_alloc = std::max<u64>(h->table_cap, (u64)kParts * h->part_slice);
     CKC(dev_alloc(h, &h->table, h->table_alloc));
     CKC(dev_alloc(h, &h->state_old, h->table_cap)); CKC(dev_alloc(h, &h->state_new, h->table_cap));
-    CKC(dev_alloc(h, &h->rec_pool, 3 * c));
-    h->recA = h->rec_pool; h->recB = h->rec_pool + c; h->recC = h->rec_pool + 2 * c;
     CKC(dev_alloc(h, &h->part_hist, (u64)kParts)); CKC(dev_alloc(h, &h->part_start, (u64)kParts + 1));
     CKC(dev_alloc(h, &h->part_nsegs, 2)); CKC(dev_alloc(h, &h->segs, (u64)kMaxSegments + kSampleSegments));
     CKC(prepare_partition(h));
-    CKC(dev_alloc(h, &h->bitmap, c / 32)); CKC(dev_alloc(h, &h->keepmap, c / 32));
-    // look-back words: one per (radix tile, digit); also one per intern tile
-    u64 min_tile = 2048;
-    h->lookback_words = std::max<u64>((c + min_tile - 1) / min_tile * kRadix, (c + kInternTile - 1) / kInternTile);
-    h->lookback_words = std::max<u64>(h->lookback_words, (c / 2048 + 1) * kParts);      // partition scatter: one word per (tile, partition)
-    CKC(dev_alloc(h, &h->lookback, h->lookback_words));
     CKC(dev_alloc(h, &h->hist, (u64)kMaxPasses * kRadix));
     CKC(dev_alloc(h, &h->ctr, 1));
-    CKC(dev_alloc(h, &h->out_idx, c)); CKC(dev_alloc(h, &h->out_ns, c));
-    CKC(dev_alloc(h, &h->out_rv, c)); CKC(dev_alloc(h, &h->out_key, c));
-    CKC(dev_alloc(h, &h->out_phase, c)); CKC(dev_alloc(h, &h->out_type, c));
+    CKC(alloc_event_buffers(h));
     CKC(dev_alloc(h, &h->d_counts_send, 4));
     CKCU(cudaMemsetAsync(h->ctr, 0, sizeof(Counters), h->stream));
-    // pads must be readable garbage-free for the vector loads past n
-    CKCU(cudaMemsetAsync(h->rv, 0, c * sizeof(u64), h->stream));
     for (int i = 0; i < 8; i++) { cudaEvent_t e; CKCU(cudaEventCreate(&e)); h->ev.push_back(e); }
     CKCU(cudaStreamSynchronize(h->stream));
 #undef CKC
@@ -561,9 +603,15 @@ int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_
     u32 words = n_allow ? max_id / 32 + 1 : 1;
     std::vector<u32> bm(words, 0u);
     for (int i = 0; i < n_allow; i++) bm[ns_allow[i] >> 5] |= 1u << (ns_allow[i] & 31);
-    if (h->ns_bitmap) { CK(h, cudaStreamSynchronize(h->stream)); CK(h, cudaFree(h->ns_bitmap)); h->ns_bitmap = nullptr; }
-    CK(h, cudaMalloc((void**)&h->ns_bitmap, words * sizeof(u32)));
-    CK(h, cudaMemcpy(h->ns_bitmap, bm.data(), words * sizeof(u32), cudaMemcpyHostToDevice));
+    // the bitmap buffer only ever grows; the copy is ordered on the engine stream like every kernel that reads it
+    if (words > h->ns_bitmap_cap) {
+        if (h->ns_bitmap) { CK(h, cudaStreamSynchronize(h->stream)); CK(h, cudaFree(h->ns_bitmap)); h->ns_bitmap = nullptr; h->ns_bitmap_cap = 0; }
+        const u32 cap = std::max<u32>(64, words * 2);
+        CK(h, cudaMalloc((void**)&h->ns_bitmap, cap * sizeof(u32)));
+        h->ns_bitmap_cap = cap;
+    }
+    h->ns_bitmap_host.assign(bm.begin(), bm.end());       // stays alive until the async copy has been consumed
+    CK(h, cudaMemcpyAsync(h->ns_bitmap, h->ns_bitmap_host.data(), words * sizeof(u32), cudaMemcpyHostToDevice, h->stream));
     h->ns_words = words;
     h->ns_filter_on = (n_allow > 0 || ns_filter_on) ? 1 : 0;
     h->critical_only = production_critical_only ? 1 : 0;
@@ -574,13 +622,16 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
                const uint8_t* phase, const uint8_t* type, uint64_t n) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
-    if (n && (!uid_hi || !uid_lo || !rv || !ns_id || !phase || !type)) FAIL(h, PTE_ERR_INVALID, "NULL column");
+    if (n && (!uid_hi || !uid_lo || !rv || !phase || !type)) FAIL(h, PTE_ERR_INVALID, "NULL column");
+    if (n && !ns_id && h->ns_filter_on) FAIL(h, PTE_ERR_INVALID, "ns_id may only be NULL while no namespace allow-list is set");
     CK(h, cudaSetDevice(h->device));
     if (n) {
         CK(h, cudaMemcpyAsync(h->uid_hi, uid_hi, n * 8, cudaMemcpyHostToDevice, h->stream));
         CK(h, cudaMemcpyAsync(h->uid_lo, uid_lo, n * 8, cudaMemcpyHostToDevice, h->stream));
         CK(h, cudaMemcpyAsync(h->rv, rv, n * 8, cudaMemcpyHostToDevice, h->stream));
-        CK(h, cudaMemcpyAsync(h->ns, ns_id, n * 4, cudaMemcpyHostToDevice, h->stream));
+        if (ns_id) CK(h, cudaMemcpyAsync(h->ns, ns_id, n * 4, cudaMemcpyHostToDevice, h->stream));
+        else if (h->ns_loaded) CK(h, cudaMemsetAsync(h->ns, 0, n * 4, h->stream));      // column absent: every event reads as namespace 0
+        h->ns_loaded = ns_id != nullptr;
         CK(h, cudaMemcpyAsync(h->phase, phase, n, cudaMemcpyHostToDevice, h->stream));
         CK(h, cudaMemcpyAsync(h->type, type, n, cudaMemcpyHostToDevice, h->stream));
         CK(h, cudaStreamSynchronize(h->stream));
@@ -667,6 +718,7 @@ int pte_generate(pte_handle h, const pte_gen_params* p) {
     const u64 n = p->n_events;
     h->n_events = n;
     h->has_run = false;
+    h->ns_loaded = true;
     if (n == 0) return PTE_OK;
     int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
     gen_fill_kernel<<<grid, 256, 0, h->stream>>>(a);
@@ -695,6 +747,11 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     h->has_run = false;
     cudaStream_t st = h->stream;
     CK(h, cudaEventRecord(h->ev[0], st));
+    if (carry && h->carry_valid && (h->pods_total + n) * 10 > h->table_cap * 7) {
+        // the stream's dictionary could pass 70 % load in this batch: drop the dead pods first (max_pods bounds LIVE pods)
+        int rb = rebuild_stream_table(h);
+        if (rb) { h->carry_valid = false; return rb; }
+    }
     const bool fresh = !(carry && h->carry_valid);       // start from an empty dictionary
     // large one-shot T-trace replays take the partition-first path (pte_partition.cuh); streams and short logs the sort path
     const bool use_part = dedupe && !carry && n && !h->force_sort && h->path_mode != 1 &&
@@ -875,6 +932,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         out->n_diff_rounds = h->n_diff_rounds;
         out->ms_pass_avg = h->pass_ev_used ? sum / h->pass_ev_used : 0.f;
         out->path = (u32)h->last_path;
+        out->n_rebuilds = h->n_rebuilds; out->ms_rebuild = h->ms_last_rebuild;
         if (use_part) {
             cudaEventElapsedTime(&out->ms_part_hist, h->ev[0], h->ev[6]);
             cudaEventElapsedTime(&out->ms_part_scatter, h->ev[6], h->ev[1]);
@@ -915,6 +973,46 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
         if (type) CK(h, cudaMemcpyAsync(type, h->out_type, n, cudaMemcpyDeviceToHost, st));
         CK(h, cudaStreamSynchronize(st));
     }
+    return PTE_OK;
+}
+
+int pte_fetch_bitmap(pte_handle h, uint32_t* words, uint64_t cap_words, uint64_t* n_emitted) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_fetch_bitmap before a successful pte_run");
+    if (!h->last_ordered) FAIL(h, PTE_ERR_STATE, "the log was pre-sorted by rv: its emit bitmap is not in arrival order, use pte_fetch");
+    const u64 need = (h->n_events + 31) / 32;
+    if (n_emitted) *n_emitted = h->last.n_emitted;
+    if (!words) return PTE_OK;
+    if (cap_words < need) FAIL(h, PTE_ERR_CAPACITY, "bitmap buffer smaller than (n_events + 31) / 32 words");
+    CK(h, cudaSetDevice(h->device));
+    if (need) {
+        CK(h, cudaMemcpyAsync(words, h->bitmap, need * sizeof(u32), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    return PTE_OK;
+}
+
+int pte_grow(pte_handle h, uint64_t max_events) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (max_events <= h->max_events) return PTE_OK;
+    if (max_events > kMaxEvents) FAIL(h, PTE_ERR_CAPACITY, "max_events above 2^30-1 per engine: shard the log by uid");
+    const u32 idx_bits = std::max<u32>(1, bitlen_host(max_events - 1));
+    if (8 + idx_bits + h->L.key_bits > 64) FAIL(h, PTE_ERR_CAPACITY, "record layout does not fit 64 bits (idx_bits + key_bits > 56)");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    void* bufs[] = {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->rec_pool, h->bitmap, h->keepmap, h->lookback,
+                    h->out_idx, h->out_ns, h->out_rv, h->out_key, h->out_phase, h->out_type,
+                    h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv, h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm};
+    for (void* b : bufs) if (b) cudaFree(b);
+    h->uid_hi = h->uid_lo = h->rv = nullptr; h->ns = nullptr; h->phase = h->type = nullptr; h->rec_pool = nullptr;
+    h->bitmap = h->keepmap = h->lookback = nullptr; h->out_idx = h->out_ns = nullptr; h->out_rv = h->out_key = nullptr;
+    h->out_phase = h->out_type = nullptr; h->shadow = LogColumns{}; h->perm = nullptr;
+    h->max_events = max_events;
+    h->L.idx_bits = idx_bits;
+    h->n_events = 0; h->has_run = false; h->key_valid = false; h->ns_loaded = true;
+    int rc = alloc_event_buffers(h);
+    if (rc) return rc;
+    CK(h, cudaStreamSynchronize(h->stream));
     return PTE_OK;
 }
 

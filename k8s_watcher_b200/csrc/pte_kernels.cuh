@@ -511,6 +511,28 @@ diff_apply_kernel(const u32* __restrict__ list, const u32* __restrict__ cnt, u64
     }
 }
 
+// ---- a dictionary that lives as long as the watch (pod_watcher.py:264-269 never ends) ------------------------
+// A stream's dictionary only ever gains uids: a DELETED pod keeps its slot with state 0.  When it fills up, the
+// slots whose state byte is not 0 (pods with a live last-known phase) are re-inserted into a fresh table and their
+// state moves with them; everything else is forgotten, which changes nothing: state 0 and "never seen" are the
+// same to the transition rule.
+__global__ void __launch_bounds__(256)
+rebuild_table_kernel(const Slot* __restrict__ old_table, const u8* __restrict__ old_state, u64 cap, Slot* __restrict__ new_table,
+                     u8* __restrict__ new_state, u32 mask, Counters* __restrict__ ctr) {
+    const u64 pol = l2_policy_evict_last();
+    u32 inserted = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (u64)gridDim.x * blockDim.x) {
+        const u32 st = old_state[i];
+        if (st == 0) continue;
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(old_table + i);
+        const u32 home = uid_home_slot(v.x, v.y, mask);
+        const u32 sl = intern_uid(new_table, mask, v.x, v.y, home, ld_slot(new_table + home, pol), inserted, &ctr->flags, pol);
+        new_state[sl] = (u8)st;
+    }
+    inserted = __reduce_add_sync(0xffffffffu, inserted);
+    if ((threadIdx.x & 31) == 0 && inserted) atomicAdd(&ctr->n_pods, inserted);
+}
+
 // ---- payload columns --------------------------------------------------------
 // Emitted records -> the columns a sink needs (idx, rv, key, ns_id, phase, type), in replay order.
 struct AssembleArgs {

@@ -296,7 +296,9 @@ class PodWatcher:
     # ---- bulk path -----------------------------------------------------------------
     def _engine_for(self, n_events: int, n_pods_hint: int) -> PhaseTransitionEngine:
         eng = self._engine
-        if eng is None or eng.max_events < n_events:
+        if eng is not None and eng.max_events < n_events and (n_pods_hint or n_events) <= eng.max_pods:
+            eng.grow(n_events)           # same dictionary, larger per-event buffers: no destroy-and-recreate
+        elif eng is None or eng.max_events < n_events or n_pods_hint > eng.max_pods:
             if eng is not None:
                 eng.close()
             eng = self._engine = PhaseTransitionEngine(max(n_events, 1024), max(n_pods_hint, 0), device=self._device)
@@ -306,11 +308,14 @@ class PodWatcher:
         """Run a whole log through the engine and return what a watcher would have notified.
         ``carry=True`` treats the log as the next batch of a stream (state kept on the device)."""
         dedupe = self.dedupe if dedupe is None else dedupe
-        if carry and self._engine is None:
-            self._engine = PhaseTransitionEngine(max(self.flush_every or len(log), len(log), 1024), self.max_pods,
-                                                 device=self._device)
-        if carry and self._engine.max_events < len(log):
-            raise ValueError("a stream batch of %d events exceeds the engine's %d" % (len(log), self._engine.max_events))
+        if carry and (self._engine is None or self._engine.max_events < len(log)):
+            # the dictionary is sized by max_pods, independently of the batch size; a longer batch than ever before
+            # moves the stream to a larger engine (pte_grow keeps dictionary and per-pod state)
+            want = max(self.flush_every or 0, len(log), 1024)
+            if self._engine is None:
+                self._engine = PhaseTransitionEngine(want, self.max_pods, device=self._device)
+            else:
+                self._engine.grow(want)
         eng = self._engine if carry else self._engine_for(len(log), max_pods)
         names = self.config.get("watcher", {}).get("namespaces", []) or []
         eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
@@ -340,13 +345,20 @@ class PodWatcher:
         self._remember(batch)
         return batch
 
+    def _stream_mode(self) -> bool:
+        return bool(self.flush_every) or self.flush_interval is not None
+
     def flush(self) -> Optional[Batch]:
         """Replay everything queued by handle_pod_event; hand the result to the sink if there is one."""
         if not self._pending:
             return None
-        log = ReplayLog.from_events(self._pending, namespaces=self._stream_namespaces)
+        # the stream's order key is the arrival number, as in the reference's loop (metadata.resource_version is
+        # neither read upstream nor ordered across the initial list of a list+watch)
+        log = ReplayLog.from_events(self._pending, namespaces=self._stream_namespaces, seq_start=self._seq + 1)
+        self._seq += len(self._pending)
         self._pending = []
-        batch = self.replay(log, carry=bool(self.flush_every))
+        self._last_flush = time.monotonic()
+        batch = self.replay(log, carry=self._stream_mode())
         if self.clusterapi_client is not None:
             sent = self.clusterapi_client.update_pod_status_batch(batch)
             if sent != len(batch):
@@ -375,12 +387,13 @@ class PodWatcher:
         try:
             for event in self.watch.stream(self.v1.list_pod_for_all_namespaces):
                 self.handle_pod_event(event["type"], event["object"])
-            self.flush()
         except KeyboardInterrupt:
             self.logger.info("Stopping Pod watcher...")
-            self.flush()
         except Exception as e:
             self.logger.error("Error in Pod watcher: %s", e)
             raise
         finally:
-            self.watch.stop()
+            try:
+                self.flush()             # whatever is still queued goes out on every exit path
+            finally:
+                self.watch.stop()

@@ -33,9 +33,12 @@ class ReplayLog:
 
     # ---- construction -------------------------------------------------------
     @classmethod
-    def from_events(cls, events: Iterable[Dict[str, Any]], namespaces: Optional[List[str]] = None) -> "ReplayLog":
+    def from_events(cls, events: Iterable[Dict[str, Any]], namespaces: Optional[List[str]] = None,
+                    seq_start: Optional[int] = None) -> "ReplayLog":
         """Intern a stream of ``{'type': str, 'object': V1Pod}`` dicts (pod_watcher.py:267-268).
-        ``namespaces`` is an optional, growing id -> name list shared between the batches of one stream."""
+        ``namespaces`` is an optional, growing id -> name list shared between the batches of one stream.
+        ``seq_start``: order the events by arrival (``rv = seq_start + i``) instead of by their
+        ``metadata.resource_version`` -- what a live watch loop wants, see PodWatcher.flush."""
         events = list(events)
         n = len(events)
         cols = {name: np.zeros(n, dt) for name, dt in COLUMNS}
@@ -53,7 +56,10 @@ class ReplayLog:
             hi, lo = codes.str_to_uid(md.uid)
             cols["uid_hi"][i], cols["uid_lo"][i] = hi, lo
             rvs = getattr(md, "resource_version", None)
-            cols["rv"][i] = int(rvs) if rvs not in (None, "") else i + 1
+            if seq_start is not None:
+                cols["rv"][i] = seq_start + i
+            else:
+                cols["rv"][i] = int(rvs) if rvs not in (None, "") else i + 1
             cols["ns_id"][i] = ns_ids.setdefault(md.namespace, len(ns_ids))
             st = pod.status
             if not st:

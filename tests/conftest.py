@@ -9,6 +9,11 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 
+# the kubernetes package is not installed here (no network): the watcher under test imports this stand-in
+import fake_kubernetes  # noqa: E402
+fake_kubernetes.install()
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
@@ -19,11 +24,6 @@ def _have_gpu() -> bool:
         return _abi.device_count() > 0
     except Exception:
         return False
-
-
-def pytest_collection_modifyitems(config, items):
-    # -m gpu on a box without a device must fail loudly, not skip: the product has no CPU path.
-    pass
 
 
 @pytest.fixture(scope="session")

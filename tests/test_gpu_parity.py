@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import fake_kubernetes as fk
+from mock_transport import MockTransport
 from k8s_watcher_b200 import PhaseTransitionEngine, PodWatcher, PteError, ReplayLog, generate_host
 from oracle import c_oracle
 from oracle import podwatch_oracle as po
@@ -393,13 +394,13 @@ def test_podwatcher_replay_matches_reference_payloads(path, monkeypatch):
 def test_live_loop_surface_with_mock_sink(monkeypatch):
     """start_watching() over a replayed stream (BASELINE config 1 shape) ends with the sink holding
     exactly the transition payloads, in order."""
-    from k8s_watcher_b200 import ClusterApiClient, _k8s_stub
+    from k8s_watcher_b200 import ClusterApiClient
+    from mock_transport import MockTransport
     fx = _load([p for p in GOLDEN if "c1_staging" in p][0])
     monkeypatch.chdir(ROOT)
     events = fk.events_from_columns(fx["cols"])
-    _k8s_stub.queue_events(events)
     fk.set_stream(events)
-    sink = ClusterApiClient("http://clusterapi.invalid")
+    sink = ClusterApiClient("http://clusterapi.invalid", transport=MockTransport())
     w = PodWatcher("staging", sink=sink)
     w.start_watching()
     keep = po.transition_filter(fx["payloads"])
@@ -453,14 +454,14 @@ def test_stream_batches_must_not_go_back_in_time():
 
 def test_live_loop_micro_batches_match_one_replay(monkeypatch):
     """start_watching() with flush_every: the sink sees exactly the transitions of the whole stream."""
-    from k8s_watcher_b200 import ClusterApiClient, _k8s_stub
+    from k8s_watcher_b200 import ClusterApiClient
+    from mock_transport import MockTransport
     fx = _load([p for p in GOLDEN if "edge_development" in p][0])
     monkeypatch.chdir(ROOT)
     events = fk.events_from_columns(fx["cols"])
-    _k8s_stub.queue_events(events)
     fk.set_stream(events)
-    sink = ClusterApiClient("http://clusterapi.invalid")
-    w = PodWatcher("staging", sink=sink, flush_every=64, max_pods=64)
+    sink = ClusterApiClient("http://clusterapi.invalid", transport=MockTransport())
+    w = PodWatcher("staging", sink=sink, flush_every=64, flush_interval=None, max_pods=64, keep_batches=None)
     cfg = dict(fx["config"])
     cfg.pop("kubernetes", None)                                    # no kubeconfig file here: default set-up path
     w.environment, w.config = "development", cfg                   # development's namespace filter
@@ -474,10 +475,9 @@ def test_live_loop_micro_batches_match_one_replay(monkeypatch):
         b.pop("event_timestamp"), want.pop("event_timestamp")
         assert b == want
     # a watcher that only keeps its last two batches alive notifies exactly the same
-    _k8s_stub.queue_events(events)
     fk.set_stream(events)
-    sink2 = ClusterApiClient("http://clusterapi.invalid")
-    w2 = PodWatcher("staging", sink=sink2, flush_every=64, max_pods=64, keep_batches=2)
+    sink2 = ClusterApiClient("http://clusterapi.invalid", transport=MockTransport())
+    w2 = PodWatcher("staging", sink=sink2, flush_every=64, flush_interval=None, max_pods=64, keep_batches=2)
     w2.environment, w2.config = "development", cfg
     w2.start_watching()
     assert len(w2.batches) == 2
@@ -491,7 +491,7 @@ def test_device_wire_bodies_match_requests_bytes(monkeypatch):
     monkeypatch.chdir(ROOT)
     log = ReplayLog.synthetic(SEED, 60_000, 700, dist=1, p_del=0.1, p_nostatus=0.05, p_null=0.05)
     log.namespaces = ['de"fault', "kube\\system", "prodüction", "monitoring", "other"]
-    sink = ClusterApiClient("http://clusterapi.invalid")
+    sink = ClusterApiClient("http://clusterapi.invalid", transport=MockTransport())
     w = PodWatcher("production", sink=sink)          # production filters: namespace list + critical-only
     w.config["watcher"]["namespaces"] = ['de"fault', "prodüction", "monitoring", "kube\\system"]
     batch = w.replay(log)

@@ -7,9 +7,10 @@ import numpy as np
 import pytest
 
 import fake_kubernetes as fk
-from k8s_watcher_b200 import (ClusterApiClient, MockTransport, PhaseTransitionEngine, PodWatcher, PteError,
+from k8s_watcher_b200 import (ClusterApiClient, PhaseTransitionEngine, PodWatcher, PteError,
                               ReplayLog, _abi, codes, generate_host, shard_of)
 from k8s_watcher_b200.clusterapi_client import ConnectionFailed, RequestTimeout, wire_body
+from mock_transport import MockTransport
 from oracle import c_oracle
 from oracle import podwatch_oracle as po
 
@@ -254,8 +255,7 @@ def test_sink_retry_timeout_and_config_factory(in_root):
 
 def test_health_gate_warns_and_continues(in_root, caplog):
     import logging
-    from k8s_watcher_b200 import _k8s_stub
-    _k8s_stub.queue_events([])
+    fk.set_stream([])
     w = PodWatcher("staging", sink=ClusterApiClient("http://h", transport=MockTransport(503)))
     with caplog.at_level(logging.WARNING):
         w.start_watching()                                         # empty stream: nothing to replay, no GPU needed

@@ -25,6 +25,9 @@ def _case(eng, n, bit_lo, n_bits, seed):
         partition_u64_static(src.array, dst.array, bit_lo, n_bits)
         want = eng.debug_sort(src.array, bit_lo, bit_lo + n_bits)      # the existing entry point
         assert np.array_equal(dst.array, want)                         # integer work: bit-exact
+        # and against numpy directly: a stable sort of the records on the digit
+        digit = (src.array >> np.uint64(bit_lo)) & np.uint64((1 << n_bits) - 1)
+        assert np.array_equal(dst.array, src.array[np.argsort(digit, kind="stable")])
     finally:
         src.free()
         dst.free()
@@ -57,3 +60,34 @@ def test_static_partition_refuses_oversize_and_bad_digits():
         with pytest.raises(PteError) as ei:
             partition_u64_static(a, a.copy(), lo, bits)
         assert ei.value.code == -1
+
+
+def test_static_partition_on_a_stream_of_the_callers():
+    """The work is issued on the stream the caller names: here one it created itself (not the default stream)."""
+    import ctypes as C
+    rt = None
+    for name in ("libcudart.so.12", "libcudart.so", "/usr/local/cuda/lib64/libcudart.so"):
+        try:
+            rt = C.CDLL(name)
+            break
+        except OSError:
+            continue
+    if rt is None:
+        pytest.skip("no shared CUDA runtime to create a stream with")
+    stream = C.c_void_p()
+    assert rt.cudaStreamCreate(C.byref(stream)) == 0
+    try:
+        rng = np.random.default_rng(11)
+        n = 123_457
+        src, dst = PinnedBuffer(n, np.uint64), PinnedBuffer(n, np.uint64)
+        try:
+            for lo, bits in ((7, 8), (40, 3)):                         # two calls in a row on that stream
+                src.array[:] = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+                partition_u64_static(src.array, dst.array, lo, bits, stream=stream.value)
+                digit = (src.array >> np.uint64(lo)) & np.uint64((1 << bits) - 1)
+                assert np.array_equal(dst.array, src.array[np.argsort(digit, kind="stable")])
+        finally:
+            src.free()
+            dst.free()
+    finally:
+        rt.cudaStreamDestroy(stream)
