@@ -171,8 +171,11 @@ int pte_read_log(pte_handle h, uint64_t* uid_hi, uint64_t* uid_lo, uint64_t* rv,
  *                           this handle, so that micro-batches of the live loop (pod_watcher.py:264-269) give
  *                           exactly the notifications one replay of the whole stream would.  A call without
  *                           the flag, or a failed call, ends the stream; the next CARRY call starts a new one.
- * Without PTE_RUN_CARRY the dictionary is cleared at the start of the call. */
-enum { PTE_RUN_DEDUPE = 1, PTE_RUN_CARRY = 2 };
+ * Without PTE_RUN_CARRY the dictionary is cleared at the start of the call.
+ * flags & PTE_RUN_BITMAP_ONLY : stop at the emit bitmap and the counts; the payload columns are not assembled
+ *                           (pte_fetch, pte_digest and pte_serialize_payloads then answer PTE_ERR_STATE).  For hosts that
+ *                           still hold the log and fetch the result with pte_fetch_bitmap. */
+enum { PTE_RUN_DEDUPE = 1, PTE_RUN_CARRY = 2, PTE_RUN_BITMAP_ONLY = 4 };
 int pte_run(pte_handle h, int flags, pte_stats* out);
 
 /* Emitted records of the last pte_run, in replay order, into caller columns (any may be NULL):
@@ -187,6 +190,18 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
  * 5 bytes per notification of pte_fetch(idx, type).  words: (n_events + 31) / 32 uint32 (NULL: only *n_emitted).
  * Not available (PTE_ERR_STATE) when the run had to pre-sort the log by rv: use pte_fetch then. */
 int pte_fetch_bitmap(pte_handle h, uint32_t* words, uint64_t cap_words, uint64_t* n_emitted);
+
+/* ingest + run + fetch_bitmap in one call, pipelined: the host columns (pinned memory for full speed) go to the device
+ * in chunks of chunk_events events (0: 2^26) on a copy stream of their own, and every chunk is replayed as the next
+ * batch of one stream (PTE_RUN_CARRY) as soon as it has landed, so the copies of the later chunks hide behind the
+ * replay of the earlier ones and the bitmap of every chunk is on its way back while the next is replayed.  Same
+ * notifications as pte_ingest + pte_run on the whole log (dedupe as in pte_run); the emit bitmap lands in
+ * bitmap_out ((n + 31) / 32 words, layout of pte_fetch_bitmap), the counts in *out (times are sums over chunks).
+ * This is the payload hand-off of pod_watcher.py:232-236 for a host that holds the log.  The log must be in
+ * resourceVersion order (PTE_ERR_UNORDERED otherwise); ns_id may be NULL as in pte_ingest.  The log stays resident. */
+int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
+                         const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n,
+                         uint64_t chunk_events, int dedupe, uint32_t* bitmap_out, pte_stats* out);
 
 /* Raise max_events of a live engine without touching the uid dictionary or the per-pod state a PTE_RUN_CARRY
  * stream carries: the live loop (pod_watcher.py:264-269) may meet a longer batch than any before.  The resident

@@ -100,6 +100,7 @@ struct pte_engine {
     u64 part_min_events = ~0ull;                             // auto mode: logs at least this long take the partition path (PTE_PART_MIN); off until it wins
     u32 seg_q8 = 304;                                        // segment length in 1/256 of the mean partition (PTE_SEG_Q8)
     int path_mode = 0;                                       // PTE_PATH: 0 auto, 1 always sort, 2 always partition
+    bool retry_after_rebuild = false;
     bool force_sort = false;                                 // one run: the partitioned attempt overflowed something
     int last_path = 0;                                       // path of the last run (0 sort, 1 partition)
     int replay_occ = 1, scatter_smem = 0, replay_smem = 0;
@@ -142,6 +143,8 @@ struct pte_engine {
     u64 *out_rv = nullptr, *out_key = nullptr;
     u8 *out_phase = nullptr, *out_type = nullptr;
     bool has_run = false;
+    bool cols_valid = false;                                 // the output columns of the last run exist (not a PTE_RUN_BITMAP_ONLY run)
+    cudaStream_t copy_stream = nullptr;                      // pte_replay_pipelined: host -> device copies run ahead of the replay
     bool ns_loaded = true;                                   // the ns column holds caller data (or generator output), not zeros
     Counters last{};
     // timing
@@ -474,7 +477,7 @@ int run_reordered(pte_engine* h, int flags, pte_stats* out) {
     std::swap(h->uid_hi, h->shadow.uid_hi); std::swap(h->uid_lo, h->shadow.uid_lo); std::swap(h->rv, h->shadow.rv);
     std::swap(h->ns, h->shadow.ns); std::swap(h->phase, h->shadow.phase); std::swap(h->type, h->shadow.type);
     h->in_reorder = true;
-    rc = pte_run(h, flags, out);
+    rc = pte_run(h, flags & ~PTE_RUN_BITMAP_ONLY, out);      // the bitmap of the sorted copy is of no use to the caller: assemble columns
     h->in_reorder = false;
     std::swap(h->uid_hi, h->shadow.uid_hi); std::swap(h->uid_lo, h->shadow.uid_lo); std::swap(h->rv, h->shadow.rv);
     std::swap(h->ns, h->shadow.ns); std::swap(h->phase, h->shadow.phase); std::swap(h->type, h->shadow.type);
@@ -515,6 +518,7 @@ void pte_destroy(pte_handle h) {
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -747,8 +751,8 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     h->has_run = false;
     cudaStream_t st = h->stream;
     CK(h, cudaEventRecord(h->ev[0], st));
-    if (carry && h->carry_valid && (h->pods_total + n) * 10 > h->table_cap * 7) {
-        // the stream's dictionary could pass 70 % load in this batch: drop the dead pods first (max_pods bounds LIVE pods)
+    if (carry && h->carry_valid && h->pods_total * 100 > h->table_cap * 65) {
+        // the stream's dictionary is past 65 % load: drop the dead pods first (max_pods bounds LIVE pods)
         int rb = rebuild_stream_table(h);
         if (rb) { h->carry_valid = false; return rb; }
     }
@@ -879,10 +883,13 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         CK(h, cudaGetLastError());
         tile_scan_kernel<<<1, 1024, 0, st>>>(h->lookback, n, h->ctr);
         CK(h, cudaGetLastError());
-        grid = (int)std::min<u64>(tiles, (u64)h->num_sms * PTE_ASM_BLOCKS);
-        assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
-        CK(h, cudaGetLastError());
-        h->n_launches += 3;
+        if (!(flags & PTE_RUN_BITMAP_ONLY)) {
+            grid = (int)std::min<u64>(tiles, (u64)h->num_sms * PTE_ASM_BLOCKS);
+            assemble_bitmap_kernel<<<grid, 256, 0, st>>>(as);
+            CK(h, cudaGetLastError());
+            h->n_launches++;
+        }
+        h->n_launches += 2;
     }
     CK(h, cudaEventRecord(h->ev[5], st));
     CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -897,6 +904,16 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         return rc2;
     }
     h->last_path = use_part ? 1 : 0;
+    if (carry && h->carry_valid && (h->last.flags & kFlagTableFull) && !(h->last.flags & kFlagBadEvent) && !h->retry_after_rebuild) {
+        // the batch brought more new uids than the dictionary had room for: make room (dead pods go) and replay the batch.
+        // Nothing of the failed attempt is kept but dictionary entries without state, which the rebuild drops.
+        int rb = rebuild_stream_table(h);
+        if (rb) { h->carry_valid = false; return rb; }
+        h->retry_after_rebuild = true;
+        int rc2 = pte_run(h, flags, out);
+        h->retry_after_rebuild = false;
+        return rc2;
+    }
     int rc = check_flags(h, h->last.flags);
     if (rc) { h->carry_valid = false; return rc; }
     if (h->last.flags & kFlagUnordered) {
@@ -910,6 +927,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     if (carry) { std::swap(h->state_old, h->state_new); h->stream_last_rv = n ? h->batch_last_rv : h->stream_last_rv; }
     h->carry_valid = carry;
     h->has_run = true;
+    h->cols_valid = !(flags & PTE_RUN_BITMAP_ONLY);
     h->key_valid = false;
     if (out) {
         memset(out, 0, sizeof(*out));
@@ -947,6 +965,7 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
               uint64_t cap, uint64_t* n_out) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_fetch before a successful pte_run");
+    if (!h->cols_valid) FAIL(h, PTE_ERR_STATE, "pte_fetch after a PTE_RUN_BITMAP_ONLY run: only pte_fetch_bitmap is available");
     const u64 n = h->last.n_emitted;
     if (n_out) *n_out = n;
     if (cap < n) FAIL(h, PTE_ERR_CAPACITY, "buffers smaller than the emitted record count");
@@ -1016,9 +1035,86 @@ int pte_grow(pte_handle h, uint64_t max_events) {
     return PTE_OK;
 }
 
+int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
+                         const uint8_t* phase, const uint8_t* type, uint64_t n, uint64_t chunk_events, int dedupe,
+                         uint32_t* bitmap_out, pte_stats* out) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
+    if (n && (!uid_hi || !uid_lo || !rv || !phase || !type || !bitmap_out)) FAIL(h, PTE_ERR_INVALID, "NULL column or bitmap");
+    if (n && !ns_id && h->ns_filter_on) FAIL(h, PTE_ERR_INVALID, "ns_id may only be NULL while no namespace allow-list is set");
+    CK(h, cudaSetDevice(h->device));
+    if (!h->copy_stream) CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    if (chunk_events == 0) chunk_events = 1ull << 26;
+    chunk_events = round_up(chunk_events, kPad);
+    const u64 n_chunks = n ? (n + chunk_events - 1) / chunk_events : 0;
+    pte_stats total;
+    memset(&total, 0, sizeof(total));
+    total.ordered = 1;
+    // every host -> device copy is queued now, on its own stream; chunk k's replay waits for chunk k's event only
+    std::vector<cudaEvent_t> landed(n_chunks);
+    cudaStream_t cs = h->copy_stream;
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (!ns_id && h->ns_loaded && n) CK(h, cudaMemsetAsync(h->ns, 0, n * 4, cs));
+    for (u64 k = 0; k < n_chunks; k++) {
+        const u64 off = k * chunk_events, len = std::min<u64>(chunk_events, n - off);
+        CK(h, cudaMemcpyAsync(h->uid_hi + off, uid_hi + off, len * 8, cudaMemcpyHostToDevice, cs));
+        CK(h, cudaMemcpyAsync(h->uid_lo + off, uid_lo + off, len * 8, cudaMemcpyHostToDevice, cs));
+        CK(h, cudaMemcpyAsync(h->rv + off, rv + off, len * 8, cudaMemcpyHostToDevice, cs));
+        if (ns_id) CK(h, cudaMemcpyAsync(h->ns + off, ns_id + off, len * 4, cudaMemcpyHostToDevice, cs));
+        CK(h, cudaMemcpyAsync(h->phase + off, phase + off, len, cudaMemcpyHostToDevice, cs));
+        CK(h, cudaMemcpyAsync(h->type + off, type + off, len, cudaMemcpyHostToDevice, cs));
+        CK(h, cudaEventCreateWithFlags(&landed[k], cudaEventDisableTiming));
+        CK(h, cudaEventRecord(landed[k], cs));
+    }
+    h->ns_loaded = ns_id != nullptr;
+    // the chunks are the batches of one stream (PTE_RUN_CARRY): the same notifications as one replay of the whole log
+    struct Saved { u64 *uid_hi, *uid_lo, *rv; u32* ns; u8 *phase, *type; u32 *bitmap, *keepmap; u64 n_events; } sv =
+        {h->uid_hi, h->uid_lo, h->rv, h->ns, h->phase, h->type, h->bitmap, h->keepmap, h->n_events};
+    h->carry_valid = false;
+    int rc = PTE_OK;
+    const int flags = (dedupe ? (PTE_RUN_DEDUPE | PTE_RUN_CARRY) : 0) | PTE_RUN_BITMAP_ONLY;
+    for (u64 k = 0; k < n_chunks && rc == PTE_OK; k++) {
+        const u64 off = k * chunk_events, len = std::min<u64>(chunk_events, n - off);
+        cudaStreamWaitEvent(h->stream, landed[k], 0);
+        h->uid_hi = sv.uid_hi + off; h->uid_lo = sv.uid_lo + off; h->rv = sv.rv + off; h->ns = sv.ns + off;
+        h->phase = sv.phase + off; h->type = sv.type + off; h->bitmap = sv.bitmap + off / 32; h->keepmap = sv.keepmap + off / 32;
+        h->n_events = len;
+        h->batch_first_rv = rv[off]; h->batch_last_rv = rv[off + len - 1];
+        if (!dedupe && k > 0 && rv[off] < rv[off - 1]) { h->err = "resourceVersion decreases between two chunks"; rc = PTE_ERR_UNORDERED; break; }
+        pte_stats st;
+        h->in_reorder = true;                                   // an unordered chunk is an error here, not a reason to pre-sort
+        rc = pte_run(h, flags, &st);
+        h->in_reorder = false;
+        if (rc == PTE_OK) {
+            cudaMemcpyAsync(bitmap_out + off / 32, h->bitmap, (len + 31) / 32 * sizeof(u32), cudaMemcpyDeviceToHost, h->stream);
+            total.n_in += st.n_in; total.n_survived += st.n_survived; total.n_emitted += st.n_emitted;
+            total.n_tombstones += st.n_tombstones; total.n_pods = st.n_pods; total.n_launches += st.n_launches;
+            total.ms_total += st.ms_total; total.ms_intern += st.ms_intern; total.ms_sort_key += st.ms_sort_key;
+            total.ms_diff += st.ms_diff; total.ms_assemble += st.ms_assemble; total.n_passes += st.n_passes;
+            total.n_rebuilds = st.n_rebuilds; total.ms_rebuild = st.ms_rebuild;
+        }
+    }
+    cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(cs);
+    for (auto e : landed) if (e) cudaEventDestroy(e);
+    h->uid_hi = sv.uid_hi; h->uid_lo = sv.uid_lo; h->rv = sv.rv; h->ns = sv.ns; h->phase = sv.phase; h->type = sv.type;
+    h->bitmap = sv.bitmap; h->keepmap = sv.keepmap;
+    h->carry_valid = false;                                     // one replay, not a stream to be continued
+    h->has_run = false;                                         // the per-chunk results were handed out already
+    h->n_events = rc == PTE_OK ? n : 0;
+    if (rc != PTE_OK) {
+        if (rc == PTE_ERR_UNORDERED)
+            h->err = "pte_replay_pipelined needs a log in resourceVersion order (use pte_ingest + pte_run, which pre-sorts): " + h->err;
+        return rc;
+    }
+    if (out) *out = total;
+    return PTE_OK;
+}
+
 int pte_digest(pte_handle h, uint64_t* out) {
     if (!h || !out) FAIL(h, PTE_ERR_INVALID, "NULL argument");
     if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_digest before a successful pte_run");
+    if (!h->cols_valid) FAIL(h, PTE_ERR_STATE, "pte_digest after a PTE_RUN_BITMAP_ONLY run: only pte_fetch_bitmap is available");
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaMemsetAsync(&h->ctr->digest, 0, sizeof(u64), h->stream));
     const u64 n = h->last.n_emitted;
@@ -1040,6 +1136,7 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
                            uint64_t* offsets, uint64_t* n_bytes) {
     if (!h || !blob || !frag_off || !n_bytes) FAIL(h, PTE_ERR_INVALID, "NULL argument");
     if (!h->has_run) FAIL(h, PTE_ERR_STATE, "pte_serialize_payloads before a successful pte_run");
+    if (!h->cols_valid) FAIL(h, PTE_ERR_STATE, "pte_serialize_payloads after a PTE_RUN_BITMAP_ONLY run: only pte_fetch_bitmap is available");
     if (first > h->last.n_emitted || count > h->last.n_emitted - first) FAIL(h, PTE_ERR_INVALID, "record range outside the emitted records");
     if (n_phase == 0 || n_ns == 0) FAIL(h, PTE_ERR_INVALID, "empty phase or namespace table");
     *n_bytes = 0;

@@ -202,11 +202,11 @@ class PhaseTransitionEngine:
         return cols
 
     # -- the hot path
-    def run(self, dedupe: bool = True, carry: bool = False) -> Dict[str, float]:
+    def run(self, dedupe: bool = True, carry: bool = False, bitmap_only: bool = False) -> Dict[str, float]:
         """Replay the resident log.  ``carry`` continues a stream: dictionary and per-pod last phase are kept
         from the previous ``carry`` run, so consecutive batches add up to one replay of the whole stream."""
         st = PteStats()
-        flags = (1 if dedupe else 0) | (2 if carry and dedupe else 0)
+        flags = (1 if dedupe else 0) | (2 if carry and dedupe else 0) | (4 if bitmap_only else 0)
         self._ck(self._L.pte_run(self._h, flags, C.byref(st)))
         self.last_stats = st.as_dict()
         return self.last_stats
@@ -265,6 +265,23 @@ class PhaseTransitionEngine:
         got = C.c_uint64()
         self._ck(self._L.pte_fetch_bitmap(self._h, _ptr(out, C.c_uint32), int(out.shape[0]), C.byref(got)))
         return out[:words]
+
+    def replay_pipelined(self, cols: Dict[str, np.ndarray], *, dedupe: bool = True, chunk_events: int = 0,
+                         with_namespaces: bool = True, bitmap_out: Optional[np.ndarray] = None):
+        """ingest + run + fetch_bitmap as one pipelined call (pte_replay_pipelined): host -> device copies of later
+        chunks overlap the replay of earlier ones.  Columns in pinned memory (PinnedBuffer) copy at full PCIe speed.
+        Returns (emit bitmap words, stats)."""
+        n = int(cols["rv"].shape[0])
+        c = {name: np.ascontiguousarray(cols[name], dtype=dt) for name, dt in COLUMNS}
+        words = (n + 31) // 32
+        out = bitmap_out if bitmap_out is not None else np.zeros(max(words, 1), np.uint32)
+        st = PteStats()
+        self._ck(self._L.pte_replay_pipelined(
+            self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64), _ptr(c["rv"], C.c_uint64),
+            _ptr(c["ns_id"], C.c_uint32) if with_namespaces else None, _ptr(c["phase"], C.c_uint8),
+            _ptr(c["type"], C.c_uint8), n, int(chunk_events), int(bool(dedupe)), _ptr(out, C.c_uint32), C.byref(st)))
+        self.last_stats = st.as_dict()
+        return out[:words], self.last_stats
 
     def grow(self, max_events: int):
         """Raise max_events in place; dictionary and carried per-pod state survive (pte_grow)."""

@@ -44,19 +44,32 @@ except ImportError:                      # no kubernetes package: replay() still
 
 from . import codes
 from .clusterapi_client import ClusterApiClient
-from .engine import EmittedColumns, PhaseTransitionEngine
+from .engine import EmittedColumns, PhaseTransitionEngine, PteError
 from .replay_log import ReplayLog
 
 
 class Batch:
     """Emitted notifications of one replay, in replay order."""
 
-    def __init__(self, watcher: "PodWatcher", log: ReplayLog, emitted: EmittedColumns, stats: Dict[str, float],
-                 dedupe: bool):
-        self.watcher, self.log, self.emitted, self.stats, self.dedupe = watcher, log, emitted, stats, dedupe
+    def __init__(self, watcher: "PodWatcher", log: ReplayLog, emitted: Optional[EmittedColumns], stats: Dict[str, float],
+                 dedupe: bool, bitmap=None):
+        self.watcher, self.log, self.stats, self.dedupe = watcher, log, stats, dedupe
+        self._emitted, self.bitmap = emitted, bitmap      # large replays come back as one bit per event (pte_fetch_bitmap)
+
+    @property
+    def emitted(self) -> EmittedColumns:
+        """Arrival index and event type of every notification (expanded from the emit bitmap on first use)."""
+        if self._emitted is None:
+            import numpy as np
+            n = len(self.log)
+            idx = np.flatnonzero(np.unpackbits(self.bitmap.view(np.uint8), bitorder="little")[:n]).astype(np.uint32)
+            z = np.empty(0, np.uint64)
+            self._emitted = EmittedColumns(idx=idx, rv=z, key=z, ns_id=np.empty(0, np.uint32), phase=np.empty(0, np.uint8),
+                                           type=self.log.columns["type"][idx])
+        return self._emitted
 
     def __len__(self):
-        return len(self.emitted)
+        return int(self.stats["n_emitted"]) if self._emitted is None else len(self._emitted)
 
     @property
     def indices(self):
@@ -68,7 +81,8 @@ class Batch:
         (rows only, no pod objects) they are serialised on the device in one call; otherwise per payload."""
         ts = event_timestamp if event_timestamp is not None else datetime.now().isoformat()
         eng = self.watcher._engine
-        if self.log._pods is None and eng is not None and self is self.watcher.batches[-1] and len(self):
+        if (self.log._pods is None and eng is not None and self.bitmap is None and self is self.watcher.batches[-1]
+                and len(self)):
             frags, n_phase, n_ns = payload_fragments(self.watcher, self.log, ts)
             buf, off = eng.serialize_payloads(frags, n_phase, n_ns)
             raw = buf.tobytes()
@@ -149,6 +163,8 @@ class PodWatcher:
         self.keep_batches = keep_batches
         # live loop: replay every `flush_every` queued events as one batch of a stream; the engine carries the
         # uid dictionary and each pod's last known phase from batch to batch (None: one replay at stream end)
+        self.pipeline_min_events = 1 << 22          # replay() pipelines logs at least this long (pte_replay_pipelined)
+        self.pipeline_chunk_events = 1 << 26
         self.flush_every = flush_every
         self.flush_interval = flush_interval
         self._last_flush = time.monotonic()
@@ -319,7 +335,21 @@ class PodWatcher:
         eng = self._engine if carry else self._engine_for(len(log), max_pods)
         names = self.config.get("watcher", {}).get("namespaces", []) or []
         eng.set_filters(log.namespace_ids(names), ns_filter_on=bool(names), critical_only=self._critical_only())
-        eng.ingest(log.columns)
+        if not carry and len(log) >= self.pipeline_min_events:
+            # a long log: copies, replay and the way back overlap chunk by chunk, and the result is one bit per event
+            # (the host holds the log, so that is all the payload hand-off needs); the namespace column stays at
+            # home when no allow-list could look at it
+            try:
+                bitmap, stats = eng.replay_pipelined(log.columns, dedupe=dedupe, with_namespaces=bool(names),
+                                                     chunk_events=self.pipeline_chunk_events,
+                                                     bitmap_out=log.bitmap_buffer())
+                batch = Batch(self, log, None, stats, dedupe, bitmap=bitmap)
+                self._remember(batch)
+                return batch
+            except PteError as e:
+                if e.code != -7:                  # PTE_ERR_UNORDERED: the plain path pre-sorts such a log
+                    raise
+        eng.ingest(log.columns, with_namespaces=bool(names) or carry)
         stats = eng.run(dedupe=dedupe, carry=carry)
         # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)

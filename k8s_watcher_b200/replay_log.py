@@ -31,6 +31,29 @@ class ReplayLog:
     def __len__(self):
         return int(self.columns["rv"].shape[0])
 
+    # ---- page-locked staging: what a host that replays big logs wants (full PCIe speed, reusable result buffer) ----
+    @classmethod
+    def pinned(cls, n_events: int, namespaces: List[str]) -> "ReplayLog":
+        """An empty log of n_events rows whose columns (and emit-bitmap buffer) live in pinned host memory
+        (pte_host_alloc); fill ``log.columns[...]`` in place."""
+        from .engine import PinnedBuffer
+        bufs = {name: PinnedBuffer(n_events, dt) for name, dt in COLUMNS}
+        log = cls({name: b.array for name, b in bufs.items()}, namespaces)
+        log._pins = bufs
+        log._bitmap_pin = PinnedBuffer((n_events + 31) // 32 + 1, np.uint32)
+        return log
+
+    def bitmap_buffer(self):
+        """Reusable destination of the emit bitmap (pinned if the log is), or None."""
+        pin = getattr(self, "_bitmap_pin", None)
+        return pin.array if pin is not None else None
+
+    def free(self):
+        for b in list(getattr(self, "_pins", {}).values()) + [getattr(self, "_bitmap_pin", None)]:
+            if b is not None:
+                b.free()
+        self._pins, self._bitmap_pin = {}, None
+
     # ---- construction -------------------------------------------------------
     @classmethod
     def from_events(cls, events: Iterable[Dict[str, Any]], namespaces: Optional[List[str]] = None,

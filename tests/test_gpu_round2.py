@@ -299,3 +299,56 @@ def test_device_wire_bodies_against_json_dumps_of_oracle_payloads(monkeypatch):
         want = po.extract_pod_data("staging", pod, ts)
         want["event_type"] = po.TYPE_NAMES[int(cols["type"][i])]
         assert b == json.dumps(want, allow_nan=False).encode("utf-8")
+
+
+# ---- pipelined replay: copies overlap the replay chunk by chunk, the result is the emit bitmap -------------------
+@pytest.mark.parametrize("env", list(FILTERS))
+@pytest.mark.parametrize("dedupe", [True, False])
+def test_pipelined_replay_equals_one_replay(env, dedupe):
+    n, pods = 250_003, 3_000
+    flt = FILTERS[env]
+    cols = c_oracle.generate(SEED + 6, n, pods, dist=1, p_del=0.06, p_nostatus=0.02, p_null=0.02)
+    want, ost, _ = c_oracle.replay(cols, critical_only=flt["critical_only"], ns_allow=flt["ns_allow"], dedupe=dedupe, pods_hint=pods)
+    with PhaseTransitionEngine(n, pods) as e:
+        e.set_filters(flt["ns_allow"], critical_only=flt["critical_only"])
+        for chunk in (8192, 65_536, 1 << 20):                    # 31 chunks, 4 chunks, one chunk
+            words, st = e.replay_pipelined(cols, dedupe=dedupe, chunk_events=chunk, with_namespaces=flt["ns_allow"] is not None)
+            bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n]
+            assert np.array_equal(np.flatnonzero(bits).astype(np.uint64), want), chunk
+            assert {k: st[k] for k in ost} == ost
+        with pytest.raises(PteError) as ei:                      # the columns were not assembled
+            e.fetch()
+        assert ei.value.code == -8
+        # a log that is not in rv order is refused here (the plain path pre-sorts it)
+        perm = np.random.default_rng(0).permutation(n)
+        with pytest.raises(PteError) as ei:
+            e.replay_pipelined({k: v[perm] for k, v in cols.items()}, dedupe=dedupe, chunk_events=65_536)
+        assert ei.value.code == -7
+
+
+def test_podwatcher_replay_pipelines_long_logs(monkeypatch):
+    monkeypatch.chdir(ROOT)
+    n, pods = 300_000, 2_000
+    cols = c_oracle.generate(SEED + 10, n, pods, dist=0, p_del=0.05)
+    log = ReplayLog.pinned(n, list(fk.NAMESPACES))
+    for k, v in cols.items():
+        log.columns[k][:] = v
+    try:
+        for envname in ("staging", "development"):
+            flt = FILTERS[envname]
+            w = PodWatcher(envname)
+            w.pipeline_min_events, w.pipeline_chunk_events = 1000, 65_536
+            batch = w.replay(log)
+            assert batch.bitmap is not None and batch.stats["n_passes"] > 3          # several chunks went through the sort
+            want, ost, _ = c_oracle.replay(cols, ns_allow=flt["ns_allow"], pods_hint=pods)
+            assert len(batch) == ost["n_emitted"]
+            assert np.array_equal(batch.indices.astype(np.uint64), want)
+            assert np.array_equal(batch.emitted.type, cols["type"][want.astype(np.int64)])
+            # the shuffled log falls back to the path that pre-sorts
+            perm = np.random.default_rng(3).permutation(n)
+            sh = ReplayLog({k: v[perm] for k, v in cols.items()}, list(fk.NAMESPACES))
+            b2 = w.replay(sh)
+            want2, _, _ = c_oracle.replay(sh.columns, ns_allow=flt["ns_allow"], pods_hint=pods)
+            assert b2.bitmap is None and np.array_equal(b2.indices.astype(np.uint64), want2)
+    finally:
+        log.free()
