@@ -4,15 +4,22 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c4] [--impl ours|reference]
 
 One step = one full replay (pte_run) of the workload's log: clear the uid dictionary, filter +
-intern + pack, LSD radix sort on the key, adjacent-diff + compaction, radix sort back to replay
-order, payload column assembly.  Default workload: BASELINE.json config 3 (the one the metric is
-quoted on): 1 B events / 10 M pods, uniform phase churn, staging filters (nothing dropped), per GPU.
+intern + pack, LSD radix sort on the interned key, segmented adjacent-diff into the emit bitmap,
+bitmap scan + compaction into the payload columns (replay order comes from the bitmap, there is no
+second sort).  Default workload: BASELINE.json config 3 (the one the metric is quoted on): 1 B events /
+10 M pods, uniform phase churn, staging filters (nothing dropped), per GPU.
 For N > 1 (launched under torchrun) every rank replays its own uid-hash shard of an N x larger
 log (weak scaling); the only collective is an NCCL all-gather of four counters per rank per step.
+--total-events T replays BASELINE config 5 literally (T = 8e9 events over the N GPUs: T / 1e9 uid-hash
+shards, each rank replays its share one after the other on one engine; generation between shards is untimed).
 
 Prints ONE JSON line (rank 0).  `value` is device time (CUDA events inside pte_run, max over
-ranks); `e2e` goes through host buffers: pte_ingest + pte_run + pte_fetch, wall clock.
---impl reference times the CPU restatement of the reference's per-event loop (oracle/) instead.
+ranks); `e2e` is PodWatcher.replay() on a log in pinned host memory: pipelined host->device copies,
+replay and the emit bitmap on its way back, wall clock.  After the timed loop every rank compares the
+count and the order-sensitive digest of its emitted records with tests/golden/digests.json (written by
+the C oracle): `parity`; a mismatch makes the run exit 1.
+--impl reference times the reference's own per-event loop on the host cores instead: the unmodified
+watcher staged in oracle/_ref when it is there (kind "reference"), else the oracle's restatement ("port").
 """
 from __future__ import annotations
 
@@ -50,6 +57,8 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--total-events", type=float, default=None,
+                    help="BASELINE config 5 literally: this many events in total over the N GPUs (e.g. 8e9)")
     return ap.parse_args()
 
 
@@ -115,15 +124,36 @@ def _cpu_worker(args):
     seed, n, pods, dist, p_del, shard, n_shards = args
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import fake_kubernetes as fk
-    from oracle import c_oracle
+    from oracle import c_oracle, make_ref
     from oracle import podwatch_oracle as po
     cols = c_oracle.generate(seed, n, pods, dist=dist, p_del=p_del, shard=shard, n_shards=n_shards)
     events = [(e["type"], e["object"]) for e in fk.events_from_columns(cols, rich=False)]
+    ref = make_ref.load_reference()
+    if ref is not None:
+        # the unmodified reference: PodWatcher.handle_pod_event per event (pod_watcher.py:214-241), payloads taken at
+        # the POST site by wrapping _extract_pod_data (the POST itself is commented out upstream), logging off
+        import logging
+        os.chdir(make_ref.DST)                     # its config paths are CWD-relative (:22,:25)
+        logging.disable(logging.CRITICAL)
+        w = ref.PodWatcher(environment="staging")
+        payloads, orig = [], w._extract_pod_data
+
+        def rec(pod):
+            d = orig(pod)
+            payloads.append(d)                     # handle_pod_event adds event_type to this same dict (:233)
+            return d
+        w._extract_pod_data = rec
+        t0 = time.perf_counter()
+        for ty, pod in events:
+            w.handle_pod_event(ty, pod)
+        keep = po.transition_filter(payloads)
+        dt = time.perf_counter() - t0
+        return n, len(keep), dt, "reference"
     t0 = time.perf_counter()
     payloads = po.reference_trace("staging", {}, events, "1970-01-01T00:00:00")
     keep = po.transition_filter(payloads)
     dt = time.perf_counter() - t0
-    return n, len(keep), dt
+    return n, len(keep), dt, "port"
 
 
 def cpu_reference_arm(wl, sample_per_core: int = 600_000):
@@ -147,20 +177,36 @@ def cpu_reference_arm(wl, sample_per_core: int = 600_000):
     t1 = time.perf_counter()
     c_oracle.generate_replay(SEED, cn, cp, dist=dist, p_del=p_del)
     c_dt = time.perf_counter() - t1
+    kind = res[0][3]
+    what = ("the unmodified reference PodWatcher.handle_pod_event (oracle/_ref) per event" if kind == "reference"
+            else "Python restatement of handle_pod_event")
     return {
-        "value": total / busy, "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": "%d events (%d per core x %d uid-hash shards, %d pods each), Python restatement of "
-                  "handle_pod_event + transition layer, logging off; pool wall %.1fs" % (total, sample_per_core, cores, pods_per, wall),
+        "value": total / busy, "unit": UNIT, "cores": cores, "kind": kind,
+        "sample": "%d events (%d per core x %d uid-hash shards, %d pods each), %s + transition layer, "
+                  "logging off; pool wall %.1fs" % (total, sample_per_core, cores, pods_per, what, wall),
         "python_1core_events_per_s": res[0][0] / res[0][2],
         "c_port_1thread_events_per_s": cn / c_dt,
         "c_port_sample": "%d events / %d pods incl. generation" % (cn, cp),
     }
 
 
+def make_config(wl, world, total_events=None):
+    """The workload description both arms print (identical keys and values for the same command line)."""
+    cfg = {"workload": wl[4], "events_per_gpu": wl[0], "pods_per_gpu": wl[1], "filters": "staging (none)",
+           "dedupe": True, "shards": world, "seed": hex(SEED),
+           "l2": "inputs (30 GB log, 8 GB record buffers) far larger than the 126 MB L2"}
+    if total_events:
+        cfg["total_events"] = int(total_events)
+        cfg["shards"] = int(total_events) // wl[0]
+        cfg["workload"] = ("BASELINE config 5: uid-hash-sharded replay %.0fB events / %.0fM pods across %d B200 (%d shards of %s)"
+                           % (total_events / 1e9, total_events / 1e8, world, cfg["shards"], wl[4].split(": ", 1)[1]))
+    return cfg
+
+
 def run_reference(args, wl, rank):
     if rank != 0:
         return
-    cfg = {"workload": wl[4], "events_per_gpu": wl[0], "pods_per_gpu": wl[1], "filters": "staging (none)"}
+    cfg = make_config(wl, int(os.environ.get("WORLD_SIZE", "1")), args.total_events)
     vals, last = [], None
     for s in range(args.warmup + args.steps):
         last = cpu_reference_arm(wl, sample_per_core=60_000)
@@ -174,8 +220,9 @@ def run_reference(args, wl, rank):
         "dtype": "python objects", "data": "synthetic", "config": cfg, "cpu_baseline": last,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-        "note": "reference arm = CPU restatement (oracle/) of the reference's per-event Python loop on a bounded "
-                "sample per step; /root/reference itself cannot travel to the GPU box",
+        "note": "reference arm = the reference's per-event Python loop on a bounded sample per step, one uid-hash shard per "
+                "host core: the unmodified watcher staged in oracle/_ref by oracle/make_ref.py when present (kind "
+                "'reference'), else the oracle's restatement (kind 'port')",
     }
     print(json.dumps(line), flush=True)
 
