@@ -255,18 +255,40 @@ def main():
         if dist_t is not None:
             dist_t.barrier()
 
+    # shards: one per GPU (weak scaling), or --total-events / events-per-shard of them dealt to the ranks in order
+    shards_total = world
+    if args.total_events:
+        shards_total = int(args.total_events) // ev
+        if shards_total * ev != int(args.total_events) or shards_total % world:
+            raise SystemExit("--total-events must be a multiple of %d events x %d GPUs" % (ev, world))
+    per_rank = shards_total // world
+    my_shards = [rank * per_rank + j for j in range(per_rank)]
+    multi = per_rank > 1
+
     eng = PhaseTransitionEngine(ev, pods, device=local)
     if world > 1:
         uid = sharding.broadcast_bytes(dist_t, PhaseTransitionEngine.comm_unique_id() if rank == 0 else None)
         eng.comm_init(uid, rank, world)
     eng.set_filters(None)                                   # staging regime: every event reaches the sort
-    eng.generate(SEED, ev, pods, dist=dist, p_del=p_del, shard=rank, n_shards=world)
+
+    def gen(g):
+        eng.generate(SEED, ev, pods, dist=dist, p_del=p_del, shard=g, n_shards=shards_total)
+    gen(my_shards[0])
 
     def step():
-        st = eng.run(dedupe=True)
-        t0 = time.perf_counter()
-        counts = eng.gather_counts() if world > 1 else None
-        return st, (time.perf_counter() - t0) * 1e3, counts
+        """One pass over this rank's shards.  With several shards per rank the next shard's log is generated in place
+        between the timed replays (inputs are resident in HBM whenever a timed region starts)."""
+        sts, g_ms, counts = [], 0.0, None
+        for g in my_shards:
+            if multi:
+                gen(g)
+            sts.append(eng.run(dedupe=True))
+            if world > 1:
+                t0 = time.perf_counter()
+                c = eng.gather_counts()
+                g_ms += (time.perf_counter() - t0) * 1e3
+                counts = c if counts is None else counts + c
+        return sts, g_ms, counts
 
     for _ in range(args.warmup):
         step()
@@ -280,12 +302,14 @@ def main():
     launches = 0
     wall0 = time.perf_counter()
     for _ in range(args.steps):
-        st, g_ms, counts = step()
-        dev_ms += st["ms_total"]; gather_ms += g_ms
-        pass_ms += st["ms_pass_avg"] * st["n_passes"]; pass_n += st["n_passes"]
-        for k in stage_sum:
-            stage_sum[k] += st[k]
-        launches += st["n_launches"]
+        sts, g_ms, counts = step()
+        gather_ms += g_ms
+        for st in sts:
+            dev_ms += st["ms_total"]
+            pass_ms += st["ms_pass_avg"] * st["n_passes"]; pass_n += st["n_passes"]
+            for k in stage_sum:
+                stage_sum[k] += st[k]
+            launches += st["n_launches"]
     barrier()
     wall_ms = (time.perf_counter() - wall0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
@@ -297,19 +321,24 @@ def main():
         total_emitted = int(counts[:, 2].sum())
     else:
         wall_step_ms = wall_ms / args.steps
-        total_events, total_emitted = int(st["n_in"]), int(st["n_emitted"])
+        total_events, total_emitted = sum(int(x["n_in"]) for x in sts), sum(int(x["n_emitted"]) for x in sts)
+
+    # ---- parity: every shard this rank replays against the C oracle's table (count + order-sensitive digest)
+    parity = _parity(eng, args, wl, my_shards, shards_total, multi, gen, sts, dist_t, world)
 
     # ---- rooflines (all HBM-bound integer kernels).  Algorithmic bytes per launch are DESIGN.md section 3's
     # per-event figures x the events one launch processes; durations are CUDA-event times inside pte_run.
     peak, peak_src = _peak()
-    traffic = _traffic()
+    traffic, traffic_src = _traffic()
     n_surv, n_emit, n_in = float(st["n_survived"]), float(st["n_emitted"]), float(st["n_in"])
-    avg = {k: v / args.steps for k, v in stage_sum.items()}
+    avg = {k: v / (args.steps * per_rank) for k, v in stage_sum.items()}       # per replay of one shard
     kp = int(st["n_passes"])
     rounds = max(1, int(st["n_diff_rounds"]))
     per_kernel = {
         # kernel: (launches per step, algorithmic bytes per launch, ms per launch)
-        "intern_pack_kernel": (1, 30.0 * n_in + 8.0 * n_surv + 16.0 * n_surv, avg["ms_intern"]),
+        # the unfiltered kernel reads uid_hi, uid_lo, rv, phase, type (26 B; ns_id is not touched), writes the record,
+        # and touches one 16-byte dictionary slot
+        "intern_pack_kernel": (1, 26.0 * n_in + 8.0 * n_surv + 16.0 * n_surv, avg["ms_intern"]),
         "radix_pass_kernel": (kp, 16.0 * n_surv, pass_ms / pass_n if pass_n else 0.0),
         "diff_flag_kernel": (rounds, 8.0 * n_surv, avg["ms_diff"] / rounds),
         "assemble_bitmap_kernel": (1, n_in / 8.0 + 14.0 * n_emit + 18.0 * n_emit, avg["ms_assemble"]),
@@ -339,6 +368,7 @@ def main():
                 "step_dram_traffic": (sum(v["launches_per_step"] * v["traffic"] for v in by_kernel.values()) if all(v["traffic"] for v in by_kernel.values()) else None),
                 "compulsory_io_bytes": 30.0 * n_in + 16.0 * n_emit,
                 "compulsory_io_frac": (30.0 * n_in + 16.0 * n_emit) / (avg["ms_total"] * 1e-3) / 1e9 / peak,
+                "traffic_source": traffic_src,
                 "note": "ms of intern/diff/assemble are stage times (kernel + its memsets)", "by_kernel": by_kernel}
 
     # ---- end to end through host buffers (rank-local; max over ranks)
@@ -346,10 +376,12 @@ def main():
     if not args.no_e2e:
         import psutil
         budget = 0.5 * psutil.virtual_memory().available / world          # all ranks share one host
-        m = ev if 35.0 * ev <= budget else max(1 << 20, int(budget / 35.0) // (1 << 20) * (1 << 20))
+        m = ev if 27.0 * ev <= budget else max(1 << 20, int(budget / 27.0) // (1 << 20) * (1 << 20))
         if world > 1:                                                      # every rank uses the same size
             m = int(sharding.gather_counts_pg(dist_t, [m, 0, 0, 0])[:, 0].min())
-        e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m)
+        numa = sharding.bind_to_gpu_numa(local) if world > 1 else None     # host thread + first-touch pinned pages next to the GPU
+        e2e = _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m, my_shards[0], shards_total)
+        e2e["numa"] = numa
         if world > 1:
             e2e["ms_per_step"] = sharding.max_over_ranks(dist_t, [e2e["ms_per_step"]])[0]
             b = sharding.gather_counts_pg(dist_t, [e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"], 0, 0])
@@ -358,6 +390,9 @@ def main():
         if world > 1:
             e2e_events = int(sharding.gather_counts_pg(dist_t, [e2e_events, 0, 0, 0])[:, 0].sum())
         e2e["value"] = sharding.throughput(e2e_events, e2e["ms_per_step"])
+        if world > 1:
+            r = sharding.gather_counts_pg(dist_t, [int(e2e["h2d_only_gbs_this_rank"] * 1000), 0, 0, 0])
+            e2e["h2d_only_gbs_all_ranks"] = float(r[:, 0].sum()) / 1000.0      # the host's measured copy ceiling at this N
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -368,9 +403,11 @@ def main():
             "metric": METRIC, "value": sharding.throughput(total_events, step_ms), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": desc, "events_per_gpu": ev, "pods_per_gpu": pods, "filters": "staging (none)",
-                       "dedupe": True, "shards": world, "l2": "inputs (30 GB log, 8 GB record buffers) far larger than the 126 MB L2",
-                       "seed": hex(SEED), "emitted_total": total_emitted, "wall_ms_per_step": wall_step_ms},
+            "config": make_config(wl, world, args.total_events),
+            "run": {"events_total": total_events, "emitted_total": total_emitted, "wall_ms_per_step": wall_step_ms,
+                    "shards_per_gpu": per_rank, "path": int(sts[-1]["path"]),
+                    "between_shards": "next shard generated in place, untimed" if multi else None},
+            "parity": parity,
             "stage_ms": {k: avg[k] for k in ("ms_intern", "ms_sort_key", "ms_diff", "ms_assemble")},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
@@ -378,6 +415,46 @@ def main():
     eng.close()
     if dist_t is not None:
         dist_t.destroy_process_group()
+    if parity["checked"] and not parity["match"]:
+        sys.exit(1)
+
+
+def _parity(eng, args, wl, my_shards, shards_total, multi, gen, last_stats, dist_t, world):
+    """Count + order-sensitive digest of the emitted records of every shard this rank replays, against
+    tests/golden/digests.json (rows written by oracle/oracle.c: orc_generate_replay via tests/golden/make_digests.py).
+    Untimed.  -> {"checked", "match", ...}; counts cover all ranks."""
+    from k8s_watcher_b200 import sharding
+    ev, pods, dist, p_del, _ = wl
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "digests.json")) as f:
+            table = json.load(f)
+    except Exception:
+        table = {"workloads": {}, "rows": {}}
+    w = table["workloads"].get(args.workload)
+    same = bool(w) and (w["events_per_shard"], w["pods_per_shard"], w["dist"], w["p_del"]) == (ev, pods, dist, p_del)
+    mine, ok, checked = {}, 0, 0
+    for j, g in enumerate(my_shards):
+        key = "%s/%d/%d" % (args.workload, shards_total, g)
+        row = table["rows"].get(key) if same else None
+        if multi:
+            gen(g)
+            st = eng.run(dedupe=True)
+        else:
+            st = last_stats[j]
+        dig = "%016x" % eng.digest()
+        good = None
+        if row is not None:
+            checked += 1
+            good = (row["digest"] == dig and all(int(st[k]) == row[k] for k in ("n_in", "n_survived", "n_emitted", "n_tombstones")))
+            ok += bool(good)
+        mine[key] = {"digest": dig, "n_emitted": int(st["n_emitted"]), "match": good}
+    tot_checked, tot_ok = checked, ok
+    if world > 1:
+        c = sharding.gather_counts_pg(dist_t, [checked, ok, 0, 0])
+        tot_checked, tot_ok = int(c[:, 0].sum()), int(c[:, 1].sum())
+    return {"checked": tot_checked > 0, "match": (tot_checked == tot_ok) if tot_checked else None,
+            "shards_checked": tot_checked, "shards_matching": tot_ok, "shards_total": shards_total,
+            "oracle": "tests/golden/digests.json (oracle/oracle.c orc_generate_replay)", "rank0": mine}
 
 
 def _key_passes(pods: int) -> int:
@@ -399,42 +476,51 @@ def _traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per launch, per kernel, from the committed ncu --set full capture."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get("dram_bytes_per_launch", {})
+            doc = json.load(f)
+        return doc.get("dram_bytes_per_launch", {}), ("static: one ncu --set full capture of this workload, not measured in this run; "
+                                                       + str(doc.get("source", "profiles/traffic.json")))
     except Exception:
-        return {}
+        return {}, None
 
 
-def _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m):
-    """What PodWatcher.replay does per batch: pte_ingest (pinned host columns -> HBM) + pte_run + pte_fetch of the
-    arrival index and event type of every notification (the host still holds the log, so that is the result).
-    All ranks share one host: if 35 B/event x events x ranks does not fit in half of the free host memory, every
-    rank runs this leg on a prefix-sized log of the same shape (same events-per-pod ratio) and says so."""
-    if m < ev:
-        _, pods, dist, p_del, _ = wl
-        eng.generate(SEED, m, max(1, int(pods * (m / ev))), dist=dist, p_del=p_del, shard=rank, n_shards=world)
-    dts = (("uid_hi", np.uint64), ("uid_lo", np.uint64), ("rv", np.uint64), ("ns_id", np.uint32), ("phase", np.uint8),
-           ("type", np.uint8))
-    pins = {k: PinnedBuffer(m, dt) for k, dt in dts}
-    host = eng.read_log(into={k: p.array for k, p in pins.items()})           # set-up, untimed
-    odts = dict(idx=np.uint32, type=np.uint8)
-    opins = {k: PinnedBuffer(m, dt) for k, dt in odts.items()}
-    out = {k: p.array for k, p in opins.items()}
-    eng.ingest(host); eng.run(); eng.fetch(columns=(), into=out)              # warm-up
+def _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m, shard=None, n_shards=None):
+    """The call a user of the drop-in makes: PodWatcher.replay(log) on a log that sits in pinned host memory
+    (ReplayLog.pinned).  Per step, inside the timed region: host -> device copies of the log's columns (26 B/event:
+    the namespace column stays at home while no allow-list is configured), the replay, and the emit bitmap back to
+    the host (1 bit/event; the host holds the log, so that is the whole result) -- pipelined chunk by chunk
+    (pte_replay_pipelined).  Also measured, for context: the plain host -> device copy rate of the same columns.
+    All ranks share one host: if the pinned log does not fit in half of the free host memory, every rank runs this
+    leg on a shorter log of the same shape (same events-per-pod ratio) and says so."""
+    from k8s_watcher_b200 import PodWatcher, ReplayLog, codes
+    shard = rank if shard is None else shard
+    n_shards = world if n_shards is None else n_shards
+    _, pods, dist, p_del, _ = wl
+    eng.generate(SEED, m, max(1, int(pods * (m / ev))), dist=dist, p_del=p_del, shard=shard, n_shards=n_shards)
+    log = ReplayLog.pinned(m, list(codes.DEFAULT_NAMESPACES))
+    eng.read_log(into=log.columns)                                            # set-up, untimed
+    w = PodWatcher("staging", engine=eng, config_dir=os.path.join(ROOT, "config"), keep_batches=1)
+    w.logger.disabled = True
+    batch = w.replay(log)                                                     # warm-up
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
-        eng.ingest(host)
-        st = eng.run(dedupe=True)
-        got = eng.fetch(columns=(), into=out)
+        batch = w.replay(log)
     ms = (time.perf_counter() - t0) * 1e3 / args.e2e_steps
     barrier()
+    # the host -> device ceiling of this box for these buffers (all ranks copying at once), untimed leg
+    t1 = time.perf_counter()
+    eng.ingest(log.columns, with_namespaces=False)
+    h2d_s = time.perf_counter() - t1
+    barrier()
     res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps, "events_per_gpu": m,
-           "h2d_bytes_per_step": 30 * m, "d2h_bytes_per_step": 5 * len(got),
-           "api": "pte_ingest + pte_run + pte_fetch(idx, type) with pinned host buffers (= PodWatcher.replay)"}
+           "h2d_bytes_per_step": 26 * m, "d2h_bytes_per_step": 4 * ((m + 31) // 32),
+           "n_emitted": len(batch), "device_ms_per_step": batch.stats["ms_total"],
+           "h2d_only_gbs_this_rank": 26.0 * m / h2d_s / 1e9,
+           "api": "PodWatcher.replay(ReplayLog in pinned memory) -> Batch (emit bitmap): pte_replay_pipelined underneath, "
+                  "chunks of %d events" % w.pipeline_chunk_events}
     if m < ev:
-        res["reduced"] = "host memory: %d ranks x 35 B x %d events do not fit in half of the free RAM; same shape, %d events per GPU" % (world, ev, m)
-    for p in list(pins.values()) + list(opins.values()):
-        p.free()
+        res["reduced"] = "host memory: %d ranks x 26 B x %d events do not fit in half of the free RAM; same shape, %d events per GPU" % (world, ev, m)
+    log.free()
     return res
 
 

@@ -63,3 +63,32 @@ def max_over_ranks(dist, values: Sequence[float]) -> List[float]:
 def throughput(total_events: int, step_ms_max: float) -> float:
     """Whole-job events/s: all ranks' events over the slowest rank's step time."""
     return total_events / (step_ms_max * 1e-3)
+
+
+def bind_to_gpu_numa(local_rank: int) -> Optional[dict]:
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off (so that pinned staging buffers, allocated
+    afterwards, are first-touched there and host -> device copies do not cross sockets).  Best effort: returns what
+    it did, or None when the topology cannot be read."""
+    import subprocess
+    try:
+        out = subprocess.run(["nvidia-smi", "-i", str(local_rank), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                             capture_output=True, text=True, timeout=10).stdout.strip()
+        bus = out.lower()
+        if bus.startswith("00000000:"):
+            bus = "0000:" + bus.split(":", 1)[1]
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return {"gpu_bus": bus, "numa_node": node, "bound": False}
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpulist = f.read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & set(os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return {"gpu_bus": bus, "numa_node": node, "cpus": cpulist, "bound": bool(allowed)}
+    except Exception:
+        return None
