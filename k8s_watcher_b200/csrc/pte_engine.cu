@@ -129,6 +129,7 @@ struct pte_engine {
     u64 lookback_words = 0;
     int pass_cfg = 0, pass_occ = 1, pass_tile = 6144;
     u64 diff_round_bytes = 64ull << 20;      // bitmap bytes one diff round may touch
+    bool full_cols_valid = false;            // out_rv / out_ns / out_phase hold the last run's records (filled on demand)
     bool key_valid = false;                  // out_key holds the keys of the last run
     bool no_invert = false;                  // PTE_NO_INVERT=1: always set emitted bits (tuning / tests)
     bool no_defer = false;                   // PTE_NO_DEFER=1: one diff launch (and one read of the records) per bitmap slice
@@ -436,6 +437,19 @@ int rebuild_stream_table(pte_engine* h) {
     std::swap(h->state_old, h->state_new);
     h->pods_total = c.n_pods;
     h->n_rebuilds++;
+    return PTE_OK;
+}
+
+// rv, namespace and phase of the emitted records are gathered from the log the first time somebody asks for them
+int ensure_full_columns(pte_engine* h) {
+    if (h->full_cols_valid) return PTE_OK;
+    const u64 n = h->last.n_emitted;
+    if (n) {
+        int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
+        emitted_columns_kernel<<<grid, 256, 0, h->stream>>>(h->out_idx, n, h->rv, h->ns, h->phase, h->out_rv, h->out_ns, h->out_phase);
+        CK(h, cudaGetLastError());
+    }
+    h->full_cols_valid = true;
     return PTE_OK;
 }
 
@@ -929,6 +943,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     h->has_run = true;
     h->cols_valid = !(flags & PTE_RUN_BITMAP_ONLY);
     h->key_valid = false;
+    h->full_cols_valid = false;
     if (out) {
         memset(out, 0, sizeof(*out));
         out->n_in = n; out->n_survived = h->last.n_survived; out->n_emitted = h->last.n_emitted;
@@ -972,6 +987,7 @@ int pte_fetch(pte_handle h, uint32_t* idx, uint64_t* rv, uint64_t* key, uint32_t
     CK(h, cudaSetDevice(h->device));
     if (n) {
         cudaStream_t st = h->stream;
+        if (rv || ns_id || phase) { int rc = ensure_full_columns(h); if (rc) return rc; }
         if (idx) CK(h, cudaMemcpyAsync(idx, h->out_idx, n * 4, cudaMemcpyDeviceToHost, st));
         if (rv) CK(h, cudaMemcpyAsync(rv, h->out_rv, n * 8, cudaMemcpyDeviceToHost, st));
         if (key) {
@@ -1120,7 +1136,7 @@ int pte_digest(pte_handle h, uint64_t* out) {
     const u64 n = h->last.n_emitted;
     if (n) {
         int grid = (int)std::min<u64>((n + 255) / 256, (u64)h->num_sms * 16);
-        digest_kernel<<<grid, 256, 0, h->stream>>>(h->out_idx, h->out_phase, h->out_type, h->uid_hi, h->uid_lo, h->rv,
+        digest_kernel<<<grid, 256, 0, h->stream>>>(h->out_idx, h->phase, h->out_type, h->uid_hi, h->uid_lo, h->rv,
                                                     h->ns, h->ctr);
         CK(h, cudaGetLastError());
     }
@@ -1143,6 +1159,7 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
     if (count == 0) { if (offsets) offsets[0] = 0; return PTE_OK; }
     CK(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
+    { int rcf = ensure_full_columns(h); if (rcf) return rcf; }
     const u64 n_frag = 9ull + n_phase + n_ns;
     if (frag_off[n_frag] != blob_len) FAIL(h, PTE_ERR_INVALID, "fragment offsets do not end at blob_len");
     int rc;

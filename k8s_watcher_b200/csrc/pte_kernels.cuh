@@ -633,19 +633,17 @@ __global__ void __launch_bounds__(256, PTE_ASM_BLOCKS) assemble_bitmap_kernel(As
         }
         __syncthreads();
         const u64 tbase = (u64)tile * kAsmTile, obase = a.lookback[tile];      // tile offsets from tile_scan_kernel
-        // kAsmRows rows per thread and iteration, all gathers issued before the first store
+        // kAsmRows rows per thread and iteration, all gathers issued before the first store.  Only the arrival index
+        // and the event type are written here (what a host that holds the log needs, pod_watcher.py:232-236); rv,
+        // namespace and phase of the emitted records are gathered on demand (emitted_columns_kernel).
         for (u32 j0 = tid; j0 < cnt; j0 += kAsmRows * 256) {
-            u32 idx[kAsmRows], ns[kAsmRows];
-            u64 rv[kAsmRows];
-            u8 ph[kAsmRows], ty[kAsmRows];
+            u32 idx[kAsmRows];
+            u8 ty[kAsmRows];
 #pragma unroll
             for (int k = 0; k < kAsmRows; k++) {
                 const u32 j = j0 + k * 256;
                 if (j < cnt) {
                     idx[k] = (u32)(tbase + s_pos[j]);
-                    rv[k] = __ldcs(a.rv + idx[k]);
-                    ns[k] = __ldcs(a.ns + idx[k]);
-                    ph[k] = __ldcs(a.phase + idx[k]);
                     ty[k] = __ldcs(a.type + idx[k]);
                 }
             }
@@ -654,8 +652,8 @@ __global__ void __launch_bounds__(256, PTE_ASM_BLOCKS) assemble_bitmap_kernel(As
                 const u32 j = j0 + k * 256;
                 if (j < cnt) {
                     const u64 o = obase + j;
-                    __stcs(a.out_idx + o, idx[k]); __stcs(a.out_rv + o, rv[k]); __stcs(a.out_ns + o, ns[k]);
-                    a.out_phase[o] = ph[k]; a.out_type[o] = ty[k];
+                    __stcs(a.out_idx + o, idx[k]);
+                    a.out_type[o] = ty[k];
                 }
             }
         }
@@ -663,16 +661,26 @@ __global__ void __launch_bounds__(256, PTE_ASM_BLOCKS) assemble_bitmap_kernel(As
     }
 }
 
+// rv, namespace and phase of the emitted records, on demand (pte_fetch of those columns, payload serialisation)
+__global__ void __launch_bounds__(256)
+emitted_columns_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict__ rv, const u32* __restrict__ ns,
+                       const u8* __restrict__ phase, u64* __restrict__ out_rv, u32* __restrict__ out_ns, u8* __restrict__ out_phase) {
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
+        const u32 i = out_idx[j];
+        out_rv[j] = rv[i]; out_ns[j] = ns[i]; out_phase[j] = phase[i];
+    }
+}
+
 // ---- digest of the emitted records (parity tool, not part of the timed path) ----
 __global__ void __launch_bounds__(256)
-digest_kernel(const u32* __restrict__ out_idx, const u8* __restrict__ out_phase, const u8* __restrict__ out_type,
+digest_kernel(const u32* __restrict__ out_idx, const u8* __restrict__ phase, const u8* __restrict__ out_type,
               const u64* __restrict__ uid_hi, const u64* __restrict__ uid_lo, const u64* __restrict__ rv,
               const u32* __restrict__ ns, Counters* __restrict__ ctr) {
     const u64 n = ctr->n_emitted;
     u64 acc = 0;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
         u32 j = out_idx[i];
-        acc += rec_digest(i, rv[j], uid_hi[j], uid_lo[j], ns[j], out_phase[i], out_type[i]);
+        acc += rec_digest(i, rv[j], uid_hi[j], uid_lo[j], ns[j], phase[j], out_type[i]);
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);

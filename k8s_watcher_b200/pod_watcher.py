@@ -349,7 +349,7 @@ class PodWatcher:
             except PteError as e:
                 if e.code != -7:                  # PTE_ERR_UNORDERED: the plain path pre-sorts such a log
                     raise
-        eng.ingest(log.columns, with_namespaces=bool(names) or carry)
+        eng.ingest(log.columns)          # with the namespace column: Batch.wire_bodies may serialise payloads on the device
         stats = eng.run(dedupe=dedupe, carry=carry)
         # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
