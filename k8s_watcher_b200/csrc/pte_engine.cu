@@ -406,6 +406,18 @@ int run_partitioned(pte_engine* h, const InternArgs& a, bool filtered) {
         cudaMemcpyToSymbol(g_rp_dbg, z, sizeof(z));
     }
 #endif
+#ifdef PTE_EXP_TRACE
+    {
+        static unsigned long long tr[64 * 8];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(tr, g_rp_trace, sizeof(tr));
+        fprintf(stderr, "tile: prober0 start-wait, tile landed, prober0 done, prober15 done, replayer0 start, replayer0 done, refill issued (us, relative)\n");
+        for (int t = 0; t < 24; t++) {
+            const unsigned long long* r = tr + t * 8; const double b = (double)tr[0];
+            fprintf(stderr, "%3d: %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f\n", t, (r[0]-b)/1e3, (r[1]-b)/1e3, (r[2]-b)/1e3, (r[6]-b)/1e3, (r[3]-b)/1e3, (r[4]-b)/1e3, (r[5]-b)/1e3);
+        }
+    }
+#endif
     pending_fixup_kernel<<<h->num_sms * 4, 256, 0, st>>>(ra.pending, ra.pending_cap, h->segs, h->seg_export, NS, h->bitmap, h->ctr);
     CK(h, cudaGetLastError());
     h->n_launches += 6;

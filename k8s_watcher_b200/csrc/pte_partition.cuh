@@ -496,11 +496,10 @@ struct ReplayArgs {
 // dynamic shared memory: [kRpStages][kRpBufRecs*3] u64 | state[slice_slots] | tags[slice_slots] | the fixed part below
 struct ReplaySmemFixed {
     unsigned short sslot[kRpStages][kRpTile];     // dictionary slot of every record of the tile
-    unsigned short queue[kRpStages][kRpTile];     // record indices grouped by replayer, arrival order inside a group
-    u32 qstart[kRpStages][kRpReplayers + 1];
-    u32 wcnt[kRpProberWarps][kRpReplayers];       // [dealing warp][queue]: count, then start
+    unsigned short queue[kRpStages][kRpTile];     // per dealing warp (kRpWarpRecs entries each): its records grouped by replayer, arrival order inside
+    unsigned short wstart[kRpStages][kRpProberWarps][kRpReplayers + 1];   // where each replayer's group starts in a dealing warp's part
+    u32 wcnt[kRpProberWarps][kRpReplayers];       // dealing warp's running count per replayer
     u8 mark[kRpReplayers][kRpMarks];              // per replayer: lane that last claimed a slot in the current step
-    u32 scan_tot[kRpReplayers];
     u64 bar_tile[kRpStages];                      // bulk copy of the stage has landed
     u64 bar_slots[kRpStages];                     // all prober warps are done with the stage
     u64 bar_done[kRpStages];                      // all replayer warps are done with the stage
@@ -534,16 +533,19 @@ __device__ __forceinline__ void replay_event(ReplayCtx& c, u32 pred, u64 meta, u
 __device__ __forceinline__ void mbar_arrive(u64* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
+// the replayer that owns a slot: slots of a line fill from its low end, so the line index is folded in
+__device__ __forceinline__ u32 slot_owner(u32 slot) { return (slot ^ (slot >> 3)) & (kRpReplayers - 1); }
 __device__ __forceinline__ void prober_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kRpProberThreads) : "memory"); }
 
-#ifdef PTE_EXP_TIMING
-__device__ unsigned long long g_rp_dbg[8];
-#define RP_MARK(v) long long v = clock64();
-#define RP_ACC(i, from, cond) if ((cond) && lane == 0) atomicAdd(&g_rp_dbg[i], (unsigned long long)(clock64() - (from)));
+#ifdef PTE_EXP_TRACE
+__device__ unsigned long long g_rp_trace[64 * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define RP_TR(slot, cond) if (blockIdx.x == 0 && (cond) && t >= 200 && t < 264 && !a.count_only && seg_iter == 1) g_rp_trace[(t - 200) * 8 + (slot)] = gtime();
 #else
+#define RP_TR(slot, cond)
+#endif
 #define RP_MARK(v)
 #define RP_ACC(i, from, cond)
-#endif
 __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
@@ -556,7 +558,7 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
     const u64 pol = l2_policy_evict_last();
     ReplayCtx cx;
     cx.a = &a; cx.invert = a.ctr->invert != 0; cx.n_emit = 0; cx.n_seen = 0; cx.seg_id = 0;
-    u32 inserted = 0;
+    u32 inserted = 0, seg_iter = 0;
     u32 par_a = 0, par_b = 0;      // phase parities, one bit per stage: probers (tile), replayers (slots, done)
 
     if (tid == 0)
@@ -573,6 +575,7 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
         const u32 seg_local = f.seg;
         if (seg_local >= n_segs) break;
         const Segment sg = a.segs[seg_local];
+        seg_iter++;
         cx.seg_id = a.first_seg + seg_local;
         const bool later = (sg.ordinal & 0x7FFFFFFFu) != 0, has_next = (sg.ordinal >> 31) != 0;
         const u32 n_rec = sg.end - sg.beg;
@@ -597,7 +600,7 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
 
         if (warp >= kRpReplayers) {
             // ---- probers: records -> dictionary slots -> the owning replayer's queue
-            const u32 pw = warp - kRpReplayers, ptid = tid - kRpReplayers * 32;
+            const u32 pw = warp - kRpReplayers;
             for (u32 t = 0; t < n_tiles; t++) {
                 const u32 sidx = t % kRpStages;
                 const u32 first = sg.beg + t * kRpTile;
@@ -606,35 +609,69 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 if (lane < kRpReplayers) f.wcnt[pw][lane] = 0;
                 __syncwarp();
                 RP_MARK(t_a)
+                RP_TR(0, pw == 0 && lane == 0)
                 mbar_wait(&f.bar_tile[sidx], (par_a >> sidx) & 1u, 128);
+                RP_TR(1, pw == 0 && lane == 0)
                 par_a ^= 1u << sidx;
                 RP_ACC(0, t_a, pw == 0)
                 RP_MARK(t_b)
-                // this warp's records are consecutive; the tagged slot of every record is loaded before any is compared
-                u32 r[kRpPerProber], cand[kRpPerProber];
+                // this warp's records are consecutive.  Lookups run in warp-wide ROUNDS: in every round each unresolved
+                // record of a thread loads its next candidate slot (the next tag of its line that carries its fingerprint),
+                // all loads of the round are in flight together, then they are compared.  Most records are done after the
+                // first round; a fingerprint shared inside a line or a uid displaced to the next line costs one more
+                // round for the whole warp -- not a dependent chain of L2 round trips per record.
+                u32 r[kRpPerProber], slot_of[kRpPerProber], line[kRpPerProber], cm[kRpPerProber];
                 u64 hi[kRpPerProber], lo[kRpPerProber];
-                ulonglong2 pv[kRpPerProber];
                 bool ok[kRpPerProber];
+                u32 pend = 0;
+                auto tag_masks = [&](u32 ln, u32 fp) -> u32 {      // bits 0..7 slots tagged fp, bits 8..15 slots tagged empty, 24..31 fp
+                    const u64 t8 = *reinterpret_cast<volatile u64*>(tags + ln * 8);
+                    const u64 sel = 0x0102040810204080ull;
+                    const u32 mm = (u32)((((bytes_equal(t8, fp) >> 7) & 0x0101010101010101ull) * sel) >> 56);
+                    const u32 me = (u32)((((bytes_equal(t8, 0) >> 7) & 0x0101010101010101ull) * sel) >> 56);
+                    return mm | (me << 8) | (fp << 24);
+                };
 #pragma unroll
                 for (int k = 0; k < kRpPerProber; k++) {
                     r[k] = pw * kRpWarpRecs + k * 32 + lane;
                     ok[k] = r[k] < valid;
                     hi[k] = ok[k] ? tb[r[k] * 3] : 0; lo[k] = ok[k] ? tb[r[k] * 3 + 1] : 0;
                     const UidHash uh = uid_hash(hi[k], lo[k], line_mask);
-                    const u64 m = ok[k] ? bytes_equal(*reinterpret_cast<volatile u64*>(tags + uh.line * 8), uh.fp) : 0ull;
-                    cand[k] = m ? uh.line * 8 + ((u32)(__ffsll((long long)m) - 1) >> 3) : 0xFFFFFFFFu;
-                    pv[k] = make_ulonglong2(0, 0);
-#ifndef PTE_EXP_NO_PROBE
-#if defined(PTE_EXP_NO_VERIFY)
-                    if (m) pv[k] = make_ulonglong2(hi[k], lo[k]);
-#elif defined(PTE_EXP_SAME_ADDR)
-                    if (m) { pv[k] = ld_slot_cg(slice + (cand[k] & 7u), pol); pv[k] = make_ulonglong2(hi[k] | (pv[k].x & 0), lo[k]); }
-#elif defined(PTE_EXP_L1)
-                    if (m) pv[k] = ld_slot(slice + cand[k], pol);
-#else
-                    if (m) pv[k] = ld_slot_cg(slice + cand[k], pol);
-#endif
-#endif
+                    line[k] = uh.line;
+                    cm[k] = ok[k] ? tag_masks(uh.line, uh.fp) : 0u;
+                    slot_of[k] = 0;
+                    pend |= ok[k] ? 1u << k : 0u;
+                }
+                while (__any_sync(0xffffffffu, pend != 0)) {
+                    u32 cand[kRpPerProber];
+                    ulonglong2 pv[kRpPerProber];
+#pragma unroll
+                    for (int k = 0; k < kRpPerProber; k++) {
+                        cand[k] = 0xFFFFFFFFu;
+                        pv[k] = make_ulonglong2(0, 0);
+                        if (((pend >> k) & 1u) && (cm[k] & 0xFFu)) {
+                            // bytes_equal may flag a byte above a true hit spuriously: a wasted load, never a wrong answer
+                            const u32 c = __ffs(cm[k] & 0xFFu) - 1;
+                            cm[k] &= ~(1u << c);
+                            cand[k] = line[k] * 8 + c;
+                            pv[k] = ld_slot_cg(slice + cand[k], pol);
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < kRpPerProber; k++) {
+                        if (!((pend >> k) & 1u)) continue;
+                        if (cand[k] != 0xFFFFFFFFu) {
+                            if (pv[k].x == hi[k] && pv[k].y == lo[k]) { slot_of[k] = cand[k]; pend &= ~(1u << k); }
+                        } else if ((cm[k] >> 8) & 0xFFu) {
+                            // no tagged candidate left and the line has a slot this CTA believes empty: a new uid (or a tag
+                            // that is stale because another CTA filled the slot) -- the full find-or-insert sorts it out
+                            slot_of[k] = intern_tagged(slice, tags, line_mask, hi[k], lo[k], inserted, &a.ctr->flags, pol);
+                            pend &= ~(1u << k);
+                        } else {
+                            line[k] = (line[k] + 1) & line_mask;       // the line is full: the uid may have been displaced to the next
+                            cm[k] = tag_masks(line[k], cm[k] >> 24);
+                        }
+                    }
                 }
                 RP_ACC(1, t_b, pw == 0)
                 RP_MARK(t_c)
@@ -642,13 +679,9 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 unsigned short lrank[kRpPerProber];
 #pragma unroll
                 for (int k = 0; k < kRpPerProber; k++) {
-                    u32 slot = 0;
-                    if (ok[k]) {
-                        if (cand[k] != 0xFFFFFFFFu && pv[k].x == hi[k] && pv[k].y == lo[k]) slot = cand[k];
-                        else slot = intern_tagged(slice, tags, line_mask, hi[k], lo[k], inserted, &a.ctr->flags, pol);
-                        f.sslot[sidx][r[k]] = (unsigned short)slot;
-                    }
-                    const u32 qq = slot & (kRpReplayers - 1);
+                    const u32 slot = slot_of[k];
+                    if (ok[k]) f.sslot[sidx][r[k]] = (unsigned short)slot;
+                    const u32 qq = slot_owner(slot);
                     u32 peers = __ballot_sync(0xffffffffu, ok[k]);
 #pragma unroll
                     for (int b = 0; b < kRpQBits; b++) {
@@ -665,36 +698,24 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                     lrank[k] = (unsigned short)(wb + __popc(before));
                     q[k] = qq;
                 }
-                RP_ACC(2, t_c, pw == 0)
-                RP_MARK(t_d)
-                prober_barrier();
-                // counts [dealing warp][queue] -> starts, queue-major: threads 0..255 hold one count each
-                u32 v = 0, incl = 0;
-                const u32 sq = ptid >> 4, sw = ptid & 15;
-                if (ptid < kRpProberWarps * kRpReplayers) {
-                    v = f.wcnt[sw][sq];
-                    incl = v;
+                __syncwarp();
+                // this warp's counts -> where each replayer's group starts inside the warp's part of the queue (no block
+                // barrier: the replayers stitch the sixteen parts together themselves)
+                {
+                    const u32 c = lane < kRpReplayers ? f.wcnt[pw][lane] : 0u;
+                    u32 ex = c;
 #pragma unroll
-                    for (int o = 1; o < 16; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, incl, o, 16); if ((lane & 15) >= (u32)o) incl += x; }
-                    if (sw == 15) f.scan_tot[sq] = incl;
+                    for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= (u32)o) ex += x; }
+                    if (lane <= kRpReplayers) f.wstart[sidx][pw][lane] = (unsigned short)(ex - c);    // lane 16: the warp's total
                 }
-                prober_barrier();
-                if (ptid < kRpProberWarps * kRpReplayers) {
-                    u32 tot = lane < kRpReplayers ? f.scan_tot[lane] : 0u, ex = tot;
-#pragma unroll
-                    for (int o = 1; o < 16; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= (u32)o) ex += x; }
-                    ex -= tot;                                                // exclusive over the queues (lanes 0..15)
-                    const u32 qbase = __shfl_sync(0xffffffffu, ex, sq);
-                    f.wcnt[sw][sq] = qbase + incl - v;
-                    if (sw == 0) f.qstart[sidx][sq] = qbase;
-                    if (ptid == 0) f.qstart[sidx][kRpReplayers] = valid;
-                }
-                prober_barrier();
+                __syncwarp();
 #pragma unroll
                 for (int k = 0; k < kRpPerProber; k++)
-                    if (ok[k]) f.queue[sidx][f.wcnt[pw][q[k]] + lrank[k]] = (unsigned short)r[k];
+                    if (ok[k]) f.queue[sidx][pw * kRpWarpRecs + f.wstart[sidx][pw][q[k]] + lrank[k]] = (unsigned short)r[k];
                 __syncwarp();
                 RP_ACC(3, t_d, pw == 0)
+                RP_TR(2, pw == 0 && lane == 0)
+                RP_TR(6, pw == 15 && lane == 0)
                 if (lane == 0) mbar_arrive(&f.bar_slots[sidx]);
             }
         } else {
@@ -706,24 +727,44 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
                 RP_MARK(t_e)
                 mbar_wait(&f.bar_slots[sidx], (par_a >> sidx) & 1u, 32);      // the probers waited for the tile's bytes
+                RP_TR(3, warp == 0 && lane == 0)
                 par_a ^= 1u << sidx;
                 RP_ACC(4, t_e, warp == 1)
                 RP_MARK(t_f)
                 const unsigned short* ss = f.sslot[sidx];
                 const unsigned short* qu = f.queue[sidx];
-                const u32 qb = f.qstart[sidx][warp], qe = f.qstart[sidx][warp + 1];
-                u32 s_next = 0xFFFF0000u | lane;
-                u64 m_next = 0;
-                if (qb + lane < qe) { const u32 rec = qu[qb + lane]; s_next = ss[rec]; m_next = tb[rec * 3 + 2]; }
-                for (u32 base = qb; base < qe; base += 32) {
+                // this replayer's records sit in sixteen groups, one per dealing warp (lane l < 16 looks after warp l's)
+                u32 g_beg = 0, g_len = 0;
+                if (lane < kRpProberWarps) {
+                    g_beg = f.wstart[sidx][lane][warp];
+                    g_len = f.wstart[sidx][lane][warp + 1] - g_beg;
+                    g_beg += lane * kRpWarpRecs;
+                }
+                u32 g_ex = g_len;
+#pragma unroll
+                for (int o = 1; o < 16; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, g_ex, o); if (lane >= (u32)o) g_ex += x; }
+                const u32 qe = __shfl_sync(0xffffffffu, g_ex, kRpProberWarps - 1);       // records of this replayer in the tile
+                g_ex -= g_len;                                                          // exclusive: first queue position of group l
+                auto fetch = [&](u32 i, u32& s_out, u64& m_out) {                       // i-th record of this replayer's queue
+                    // the group that holds position i: the last one that starts at or before i (binary search over lanes 0..15)
+                    u32 g = 0;
+#pragma unroll
+                    for (int step = kRpProberWarps / 2; step; step >>= 1) {
+                        const u32 probe = __shfl_sync(0xffffffffu, g_ex, g + step);
+                        if (probe <= i) g += step;
+                    }
+                    const u32 gb = __shfl_sync(0xffffffffu, g_beg, g), ge = __shfl_sync(0xffffffffu, g_ex, g);
+                    s_out = 0xFFFF0000u | lane; m_out = 0;
+                    if (i < qe) { const u32 rec = qu[gb + (i - ge)]; s_out = ss[rec]; m_out = tb[rec * 3 + 2]; }
+                };
+                u32 s_next;
+                u64 m_next;
+                fetch(lane, s_next, m_next);
+                for (u32 base = 0; base < qe; base += 32) {
                     const bool active = base + lane < qe;
                     const u32 s = s_next;
                     const u64 meta = m_next;
-                    if (base + 32 < qe) {                                     // next step's operands, off the chain
-                        const u32 in = base + 32 + lane;
-                        s_next = 0xFFFF0000u | lane; m_next = 0;
-                        if (in < qe) { const u32 rec = qu[in]; s_next = ss[rec]; m_next = tb[rec * 3 + 2]; }
-                    }
+                    if (base + 32 < qe) fetch(base + 32 + lane, s_next, m_next);      // next step's operands, off the chain
                     const u32 tp = (u32)meta & 0xFFu;
                     const u32 h = (s >> kRpQBits) & (kRpMarks - 1);
                     if (active) mark[h] = (u8)lane;
@@ -746,10 +787,12 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                     __syncwarp();                                             // this step's state before the next step's loads
                 }
                 RP_ACC(5, t_f, warp == 1)
+                RP_TR(4, warp == 0 && lane == 0)
                 if (lane == 0) mbar_arrive(&f.bar_done[sidx]);
                 if (warp == 0 && t + kRpStages < n_tiles) {
                     // the stage is free once every replayer is done with it: refill
                     mbar_wait(&f.bar_done[sidx], (par_b >> sidx) & 1u, 32);
+                    RP_TR(5, lane == 0)
                     if (lane == 0) issue(t + kRpStages);
                 }
                 if (warp == 0) par_b ^= 1u << sidx;
