@@ -394,27 +394,16 @@ int run_partitioned(pte_engine* h, const InternArgs& a, bool filtered) {
     ra.segs = h->segs; ra.n_segs = h->part_nsegs; ra.first_seg = 0; ra.count_only = 0;
     part_replay_kernel<<<h->num_sms * h->replay_occ, kRpThreads, h->replay_smem, st>>>(ra);
     CK(h, cudaGetLastError());
-#ifdef PTE_EXP_TIMING
-    {
-        unsigned long long d[8];
-        cudaStreamSynchronize(st);
-        cudaMemcpyFromSymbol(d, g_rp_dbg, sizeof(d));
-        const double k = 1.0 / 148.0 / 1.9e6;
-        fprintf(stderr, "replay timing per CTA (ms): prober0 wait-tile %.2f probe-issue %.2f resolve+deal %.2f barriers+queue %.2f | replayer1 wait %.2f steps %.2f\n",
-                d[0] * k, d[1] * k, d[2] * k, d[3] * k, d[4] * k, d[5] * k);
-        unsigned long long z[8] = {0};
-        cudaMemcpyToSymbol(g_rp_dbg, z, sizeof(z));
-    }
-#endif
-#ifdef PTE_EXP_TRACE
+#ifdef PTE_EXP_TRACE      // development build (-DPTE_EXP_TRACE): time stamps of one CTA's pipeline, tiles 200..223 of its first segment
     {
         static unsigned long long tr[64 * 8];
         cudaStreamSynchronize(st);
         cudaMemcpyFromSymbol(tr, g_rp_trace, sizeof(tr));
-        fprintf(stderr, "tile: prober0 start-wait, tile landed, prober0 done, prober15 done, replayer0 start, replayer0 done, refill issued (us, relative)\n");
+        fprintf(stderr, "tile: prober0 start-wait, tile landed, prober0 done, LAST prober done, replayer0 start, replayer0 done, LAST replayer done, refill issued (us, relative)\n");
         for (int t = 0; t < 24; t++) {
             const unsigned long long* r = tr + t * 8; const double b = (double)tr[0];
-            fprintf(stderr, "%3d: %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f\n", t, (r[0]-b)/1e3, (r[1]-b)/1e3, (r[2]-b)/1e3, (r[6]-b)/1e3, (r[3]-b)/1e3, (r[4]-b)/1e3, (r[5]-b)/1e3);
+            fprintf(stderr, "%3d: %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f %8.2f\n", t, (r[0]-b)/1e3, (r[1]-b)/1e3, (r[2]-b)/1e3, (r[6]-b)/1e3, (r[3]-b)/1e3, (r[4]-b)/1e3, (r[7]-b)/1e3, (r[5]-b)/1e3);
+            if (t == 23) { unsigned long long z[64 * 8] = {0}; cudaMemcpyToSymbol(g_rp_trace, z, sizeof(z)); }
         }
     }
 #endif

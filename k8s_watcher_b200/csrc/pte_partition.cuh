@@ -440,12 +440,7 @@ __device__ u32 intern_tagged(Slot* __restrict__ slice, u8* tags, u32 line_mask, 
         const u64 e8 = bytes_equal(t8, 0);
         if (e8) {
             const u32 e = (u32)(__ffsll((long long)e8) - 1) >> 3;
-#ifdef PTE_EXP_NO_CAS
-            const ulonglong2 old = make_ulonglong2(0, 0);
-            slice[line * 8 + e].hi = hi; slice[line * 8 + e].lo = lo;
-#else
             const ulonglong2 old = cas128(slice + line * 8 + e, 0, 0, hi, lo);
-#endif
             if (old.x == 0 && old.y == 0) { tags[line * 8 + e] = (u8)uh.fp; inserted++; return line * 8 + e; }
             tags[line * 8 + e] = (u8)uid_hash(old.x, old.y, line_mask).fp;       // filled by somebody else: repair the tag
             if (old.x == hi && old.y == lo) return line * 8 + e;
@@ -524,9 +519,7 @@ __device__ __forceinline__ void replay_event(ReplayCtx& c, u32 pred, u64 meta, u
     } else {
         const bool e = emits(pred, tp);
         c.n_emit += e; c.n_seen++;
-#ifndef PTE_EXP_NO_FLIP
         if (!a.count_only && e != c.invert) flip_bit(a.bitmap, (u32)(meta >> 8));
-#endif
     }
 }
 
@@ -541,11 +534,11 @@ __device__ __forceinline__ void prober_barrier() { asm volatile("bar.sync 1, %0;
 __device__ unsigned long long g_rp_trace[64 * 8];
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define RP_TR(slot, cond) if (blockIdx.x == 0 && (cond) && t >= 200 && t < 264 && !a.count_only && seg_iter == 1) g_rp_trace[(t - 200) * 8 + (slot)] = gtime();
+#define RP_TRMAX(slot, cond) if (blockIdx.x == 0 && (cond) && t >= 200 && t < 264 && !a.count_only && seg_iter == 1) atomicMax(&g_rp_trace[(t - 200) * 8 + (slot)], gtime());
 #else
 #define RP_TR(slot, cond)
+#define RP_TRMAX(slot, cond)
 #endif
-#define RP_MARK(v)
-#define RP_ACC(i, from, cond)
 __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* buf = reinterpret_cast<u64*>(smem_raw);
@@ -608,13 +601,10 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
                 if (lane < kRpReplayers) f.wcnt[pw][lane] = 0;
                 __syncwarp();
-                RP_MARK(t_a)
                 RP_TR(0, pw == 0 && lane == 0)
                 mbar_wait(&f.bar_tile[sidx], (par_a >> sidx) & 1u, 128);
                 RP_TR(1, pw == 0 && lane == 0)
                 par_a ^= 1u << sidx;
-                RP_ACC(0, t_a, pw == 0)
-                RP_MARK(t_b)
                 // this warp's records are consecutive.  Lookups run in warp-wide ROUNDS: in every round each unresolved
                 // record of a thread loads its next candidate slot (the next tag of its line that carries its fingerprint),
                 // all loads of the round are in flight together, then they are compared.  Most records are done after the
@@ -673,8 +663,6 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                         }
                     }
                 }
-                RP_ACC(1, t_b, pw == 0)
-                RP_MARK(t_c)
                 u32 q[kRpPerProber];
                 unsigned short lrank[kRpPerProber];
 #pragma unroll
@@ -713,9 +701,8 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 for (int k = 0; k < kRpPerProber; k++)
                     if (ok[k]) f.queue[sidx][pw * kRpWarpRecs + f.wstart[sidx][pw][q[k]] + lrank[k]] = (unsigned short)r[k];
                 __syncwarp();
-                RP_ACC(3, t_d, pw == 0)
                 RP_TR(2, pw == 0 && lane == 0)
-                RP_TR(6, pw == 15 && lane == 0)
+                RP_TRMAX(6, lane == 0)
                 if (lane == 0) mbar_arrive(&f.bar_slots[sidx]);
             }
         } else {
@@ -725,12 +712,9 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 const u32 sidx = t % kRpStages;
                 const u32 first = sg.beg + t * kRpTile;
                 const u64* tb = buf + sidx * kRpBufRecs * 3 + (first & 1u) * 3;
-                RP_MARK(t_e)
                 mbar_wait(&f.bar_slots[sidx], (par_a >> sidx) & 1u, 32);      // the probers waited for the tile's bytes
                 RP_TR(3, warp == 0 && lane == 0)
                 par_a ^= 1u << sidx;
-                RP_ACC(4, t_e, warp == 1)
-                RP_MARK(t_f)
                 const unsigned short* ss = f.sslot[sidx];
                 const unsigned short* qu = f.queue[sidx];
                 // this replayer's records sit in sixteen groups, one per dealing warp (lane l < 16 looks after warp l's)
@@ -786,8 +770,8 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                     if (active) replay_event(cx, pred, meta, s);
                     __syncwarp();                                             // this step's state before the next step's loads
                 }
-                RP_ACC(5, t_f, warp == 1)
                 RP_TR(4, warp == 0 && lane == 0)
+                RP_TRMAX(7, lane == 0)
                 if (lane == 0) mbar_arrive(&f.bar_done[sidx]);
                 if (warp == 0 && t + kRpStages < n_tiles) {
                     // the stage is free once every replayer is done with it: refill
