@@ -203,6 +203,14 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
                          const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n,
                          uint64_t chunk_events, int dedupe, uint32_t* bitmap_out, pte_stats* out);
 
+/* One batch of a live stream (the body of `for event in stream`, pod_watcher.py:266-269, for a micro-batch) in one call:
+ * pte_ingest + pte_run(flags, normally PTE_RUN_DEDUPE | PTE_RUN_CARRY) + pte_fetch(idx, type), with one host
+ * synchronisation instead of three.  idx_out / type_out (capacity cap) receive the arrival index and the event type of
+ * every notification of the batch; *out the counts.  Afterwards the engine is in the state pte_run leaves it in. */
+int pte_stream_batch(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
+                     const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n, int flags,
+                     uint32_t* idx_out, uint8_t* type_out, uint64_t cap, pte_stats* out);
+
 /* Raise max_events of a live engine without touching the uid dictionary or the per-pod state a PTE_RUN_CARRY
  * stream carries: the live loop (pod_watcher.py:264-269) may meet a longer batch than any before.  The resident
  * log and the results of the last run are dropped; ingest again.  No-op when max_events is not larger. */

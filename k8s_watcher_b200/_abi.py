@@ -64,6 +64,8 @@ SYMBOLS = {
     "pte_fetch": (C.c_int, [C.c_void_p, _u32p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, _u64p]),
     "pte_fetch_bitmap": (C.c_int, [C.c_void_p, _u32p, C.c_uint64, _u64p]),
     "pte_grow": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "pte_stream_batch": (C.c_int, [C.c_void_p, _u64p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, C.c_int, _u32p, _u8p,
+                                   C.c_uint64, C.POINTER(PteStats)]),
     "pte_replay_pipelined": (C.c_int, [C.c_void_p, _u64p, _u64p, _u64p, _u32p, _u8p, _u8p, C.c_uint64, C.c_uint64, C.c_int,
                                        _u32p, C.POINTER(PteStats)]),
     "pte_digest": (C.c_int, [C.c_void_p, _u64p]),

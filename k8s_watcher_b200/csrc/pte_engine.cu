@@ -637,8 +637,36 @@ int pte_set_filters(pte_handle h, const uint32_t* ns_allow, int n_allow, int ns_
     return PTE_OK;
 }
 
+static int ingest_impl(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
+                       const uint8_t* phase, const uint8_t* type, uint64_t n, bool sync);
+
 int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
                const uint8_t* phase, const uint8_t* type, uint64_t n) {
+    return ingest_impl(h, uid_hi, uid_lo, rv, ns_id, phase, type, n, true);
+}
+
+// One batch of a live stream in ONE call: copy in, replay as the next PTE_RUN_CARRY batch, arrival index + event type of
+// the notifications out.  Same as pte_ingest + pte_run + pte_fetch(idx, type) with two host synchronisations less.
+int pte_stream_batch(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
+                     const uint8_t* phase, const uint8_t* type, uint64_t n, int flags, uint32_t* idx_out, uint8_t* type_out,
+                     uint64_t cap, pte_stats* out) {
+    int rc = ingest_impl(h, uid_hi, uid_lo, rv, ns_id, phase, type, n, false);
+    if (rc) return rc;
+    pte_stats st;
+    rc = pte_run(h, flags & ~PTE_RUN_BITMAP_ONLY, &st);      // synchronises the stream: the host columns are free again
+    if (rc) return rc;
+    if (out) *out = st;
+    if (st.n_emitted > cap) FAIL(h, PTE_ERR_CAPACITY, "buffers smaller than the emitted record count");
+    if (st.n_emitted && (idx_out || type_out)) {
+        if (idx_out) CK(h, cudaMemcpyAsync(idx_out, h->out_idx, st.n_emitted * 4, cudaMemcpyDeviceToHost, h->stream));
+        if (type_out) CK(h, cudaMemcpyAsync(type_out, h->out_type, st.n_emitted, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
+    return PTE_OK;
+}
+
+static int ingest_impl(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
+                       const uint8_t* phase, const uint8_t* type, uint64_t n, bool sync) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
     if (n && (!uid_hi || !uid_lo || !rv || !phase || !type)) FAIL(h, PTE_ERR_INVALID, "NULL column");
@@ -653,7 +681,7 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
         h->ns_loaded = ns_id != nullptr;
         CK(h, cudaMemcpyAsync(h->phase, phase, n, cudaMemcpyHostToDevice, h->stream));
         CK(h, cudaMemcpyAsync(h->type, type, n, cudaMemcpyHostToDevice, h->stream));
-        CK(h, cudaStreamSynchronize(h->stream));
+        if (sync) CK(h, cudaStreamSynchronize(h->stream));
     }
     h->n_events = n;
     h->has_run = false;

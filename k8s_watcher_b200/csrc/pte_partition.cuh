@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                 u32 r[kRpPerProber], slot_of[kRpPerProber], line[kRpPerProber], cm[kRpPerProber];
                 u64 hi[kRpPerProber], lo[kRpPerProber];
                 bool ok[kRpPerProber];
-                u32 pend = 0;
+                u32 pend = 0, walked = 0;
                 auto tag_masks = [&](u32 ln, u32 fp) -> u32 {      // bits 0..7 slots tagged fp, bits 8..15 slots tagged empty, 24..31 fp
                     const u64 t8 = *reinterpret_cast<volatile u64*>(tags + ln * 8);
                     const u64 sel = 0x0102040810204080ull;
@@ -656,6 +656,10 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                             // no tagged candidate left and the line has a slot this CTA believes empty: a new uid (or a tag
                             // that is stale because another CTA filled the slot) -- the full find-or-insert sorts it out
                             slot_of[k] = intern_tagged(slice, tags, line_mask, hi[k], lo[k], inserted, &a.ctr->flags, pol);
+                            pend &= ~(1u << k);
+                        } else if (++walked > 4 * (line_mask + 1)) {
+                            // every line of the slice is full and none holds the uid: more pods than the slice has room for
+                            atomicOr(&a.ctr->flags, kFlagTableFull);       // the run is repeated on the sort path
                             pend &= ~(1u << k);
                         } else {
                             line[k] = (line[k] + 1) & line_mask;       // the line is full: the uid may have been displaced to the next

@@ -283,6 +283,22 @@ class PhaseTransitionEngine:
         self.last_stats = st.as_dict()
         return out[:words], self.last_stats
 
+    def stream_batch(self, cols: Dict[str, np.ndarray], *, dedupe: bool = True, carry: bool = True):
+        """One micro-batch of a live stream in one call (pte_stream_batch): -> (EmittedColumns with idx and type, stats)."""
+        n = int(cols["rv"].shape[0])
+        c = {name: np.ascontiguousarray(cols[name], dtype=dt) for name, dt in COLUMNS}
+        idx, ty = np.empty(n, np.uint32), np.empty(n, np.uint8)
+        st = PteStats()
+        flags = (1 if dedupe else 0) | (2 if carry and dedupe else 0)
+        self._ck(self._L.pte_stream_batch(
+            self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64), _ptr(c["rv"], C.c_uint64),
+            _ptr(c["ns_id"], C.c_uint32), _ptr(c["phase"], C.c_uint8), _ptr(c["type"], C.c_uint8), n, flags,
+            _ptr(idx, C.c_uint32), _ptr(ty, C.c_uint8), n, C.byref(st)))
+        self.last_stats = st.as_dict()
+        k = int(st.n_emitted)
+        z = np.empty(0, np.uint64)
+        return EmittedColumns(idx=idx[:k], rv=z, key=z, ns_id=np.empty(0, np.uint32), phase=np.empty(0, np.uint8), type=ty[:k]), self.last_stats
+
     def grow(self, max_events: int):
         """Raise max_events in place; dictionary and carried per-pod state survive (pte_grow)."""
         self._ck(self._L.pte_grow(self._h, int(max_events)))

@@ -349,6 +349,12 @@ class PodWatcher:
             except PteError as e:
                 if e.code != -7:                  # PTE_ERR_UNORDERED: the plain path pre-sorts such a log
                     raise
+        if carry:
+            # a micro-batch of the live loop: copy in, replay, notifications out in one call
+            emitted, stats = eng.stream_batch(log.columns, dedupe=dedupe, carry=True)
+            batch = Batch(self, log, emitted, stats, dedupe)
+            self._remember(batch)
+            return batch
         eng.ingest(log.columns)          # with the namespace column: Batch.wire_bodies may serialise payloads on the device
         stats = eng.run(dedupe=dedupe, carry=carry)
         # the host holds the log, so the arrival index (+ event type) is all the payload hand-off needs
