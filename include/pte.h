@@ -143,6 +143,10 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
  * 0-based number, and the log is left empty. */
 int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line);
 
+/* Device time of the last pte_ingest_json (CUDA events on the engine stream, host <-> device copies excluded):
+ * the line index (count, scan, list of newlines) and the scanner kernel; text_bytes = size of that log. */
+int pte_json_timing(pte_handle h, float* ms_index, float* ms_parse, uint64_t* text_bytes);
+
 /* Dictionary of the last pte_ingest_json: which = 0 namespaces (index = ns_id), 1 phase strings (index = code - 7).
  * Strings are written back to back into buf, offsets[0..n] delimit them; buf == NULL just counts (*n_out). */
 int pte_json_strings(pte_handle h, int which, char* buf, uint64_t cap, uint32_t* offsets, uint32_t max_entries,
@@ -228,6 +232,9 @@ int pte_grow(pte_handle h, uint64_t max_events);
 int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const char* blob, uint32_t blob_len,
                            const uint32_t* frag_off, uint32_t n_phase, uint32_t n_ns, char* out, uint64_t out_cap,
                            uint64_t* offsets, uint64_t* n_bytes);
+
+/* Device time of the kernel that wrote the bodies of the last pte_serialize_payloads (CUDA events, copies excluded). */
+int pte_payload_timing(pte_handle h, float* ms_write, uint64_t* body_bytes);
 
 /* Order-sensitive 64-bit digest of the emitted records (position, rv, uid, ns, phase, type);
  * same arithmetic as oracle/oracle.c rec_digest.  For parity at sizes too big to compare in full. */

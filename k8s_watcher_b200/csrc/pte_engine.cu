@@ -122,6 +122,8 @@ struct pte_engine {
     u32 *json_err = nullptr, *json_ns_remap = nullptr; u8* json_ph_remap = nullptr;
     std::vector<std::string> json_names[2];                  // [0] namespaces by ns_id, [1] phase strings for codes >= 7
     u64* d_minmax = nullptr;
+    float ms_payload = 0.f; u64 payload_bytes = 0;            // device time of the last payload_write_kernel
+    float ms_json[2] = {0.f, 0.f}; u64 json_bytes = 0;        // device times of the last pte_ingest_json
     bool in_reorder = false;
     u32 last_ordered = 1;
     u64 pods_total = 0, stream_last_rv = 0, batch_first_rv = 0, batch_last_rv = 0;
@@ -1213,13 +1215,17 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
     if (!out || !offsets) return PTE_OK;                       // size query
     if (total > out_cap) FAIL(h, PTE_ERR_CAPACITY, "output buffer smaller than the serialised payloads (size in *n_bytes)");
     if ((rc = grow(h, &h->pay_buf, &h->pay_buf_cap, total + 64))) return rc;
+    CK(h, cudaEventRecord(h->ev[3], st));
     payload_write_kernel<<<grid, 256, 0, st>>>(t, h->out_idx, h->out_ns, h->out_phase, h->out_type, h->uid_hi, h->uid_lo,
                                                 first, count, h->pay_tile_off, h->pay_buf, h->pay_rec_off);
     CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev[4], st));
     CK(h, cudaMemcpyAsync(out, h->pay_buf, total, cudaMemcpyDeviceToHost, st));
     CK(h, cudaMemcpyAsync(offsets, h->pay_rec_off, count * sizeof(u64), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
     offsets[count] = total;
+    cudaEventElapsedTime(&h->ms_payload, h->ev[3], h->ev[4]);
+    h->payload_bytes = total;
     return PTE_OK;
 }
 
@@ -1243,6 +1249,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     if ((rc = grow(h, &h->json_chunk_cnt, &h->json_chunk_cap, chunks))) return rc;
     if ((rc = grow(h, &h->pay_tile_off, &h->pay_tile_cap, chunks + 1))) return rc;
     int grid = (int)std::min<u64>(chunks, (u64)h->num_sms * 8);
+    CK(h, cudaEventRecord(h->ev[0], st));
     json_count_newlines_kernel<<<grid, 256, 0, st>>>(h->json_text, len, h->json_chunk_cnt);
     CK(h, cudaGetLastError());
     scan_u32_to_u64_kernel<<<1, 1024, 0, st>>>(h->json_chunk_cnt, chunks, h->pay_tile_off);
@@ -1261,7 +1268,8 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
         CK(h, cudaMalloc((void**)&h->json_ns_off, kJsonNsSlots * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_ph_keys, kJsonPhSlots * sizeof(u64)));
         CK(h, cudaMalloc((void**)&h->json_ph_off, kJsonPhSlots * sizeof(u32)));
-        CK(h, cudaMalloc((void**)&h->json_err, 2 * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_err, 4 * sizeof(u32)));
+        CK(h, cudaFuncSetAttribute(json_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kJsonWarps * (kJsonWindow + 16)));
         CK(h, cudaMalloc((void**)&h->json_ns_remap, kJsonNsSlots * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_ph_remap, kJsonPhSlots));
     }
@@ -1269,7 +1277,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaMemsetAsync(h->json_ns_off, 0xFF, kJsonNsSlots * sizeof(u32), st));
     CK(h, cudaMemsetAsync(h->json_ph_keys, 0, kJsonPhSlots * sizeof(u64), st));
     CK(h, cudaMemsetAsync(h->json_ph_off, 0xFF, kJsonPhSlots * sizeof(u32), st));
-    const u32 err_init[2] = {0u, 0xFFFFFFFFu};
+    const u32 err_init[4] = {0u, 0xFFFFFFFFu, 0u, 0u};        // [2] is the parse kernel's line-group ticket
     CK(h, cudaMemcpyAsync(h->json_err, err_init, sizeof(err_init), cudaMemcpyHostToDevice, st));
     JsonArgs a;
     a.text = h->json_text; a.len = len; a.nl = h->json_nl; a.n_lines = n_lines; a.n_nl = n_nl;
@@ -1277,9 +1285,11 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     a.ns_dict = StrDict{h->json_ns_keys, h->json_ns_off, kJsonNsSlots - 1};
     a.phase_dict = StrDict{h->json_ph_keys, h->json_ph_off, kJsonPhSlots - 1};
     a.err = h->json_err;
-    grid = (int)std::min<u64>((n_lines + 127) / 128, (u64)h->num_sms * 16);
-    json_parse_kernel<<<grid, 128, 0, st>>>(a);
+    grid = (int)std::min<u64>((n_lines + 127) / 128, (u64)h->num_sms * 2);
+    CK(h, cudaEventRecord(h->ev[1], st));
+    json_parse_kernel<<<grid, kJsonWarps * 32, kJsonWarps * (kJsonWindow + 16), st>>>(a, h->json_err + 2);
     CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev[2], st));
     u32 err[2];
     CK(h, cudaMemcpyAsync(err, h->json_err, sizeof(err), cudaMemcpyDeviceToHost, st));
     std::vector<u64> nk(kJsonNsSlots), pk(kJsonPhSlots);
@@ -1329,7 +1339,25 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaStreamSynchronize(st));
     h->n_events = n_lines;
     h->batch_first_rv = ends[0]; h->batch_last_rv = ends[1];
+    cudaEventElapsedTime(&h->ms_json[0], h->ev[0], h->ev[1]);       // line index (count, scan, list) + dictionary set-up
+    cudaEventElapsedTime(&h->ms_json[1], h->ev[1], h->ev[2]);       // json_parse_kernel
+    h->json_bytes = len;
     if (n_events) *n_events = n_lines;
+    return PTE_OK;
+}
+
+int pte_payload_timing(pte_handle h, float* ms_write, uint64_t* body_bytes) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (ms_write) *ms_write = h->ms_payload;
+    if (body_bytes) *body_bytes = h->payload_bytes;
+    return PTE_OK;
+}
+
+int pte_json_timing(pte_handle h, float* ms_index, float* ms_parse, uint64_t* text_bytes) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    if (ms_index) *ms_index = h->ms_json[0];
+    if (ms_parse) *ms_parse = h->ms_json[1];
+    if (text_bytes) *text_bytes = h->json_bytes;
     return PTE_OK;
 }
 

@@ -169,6 +169,18 @@ class PhaseTransitionEngine:
         self._ck(self._L.pte_ingest_json(self._h, text, len(text), C.byref(n), C.byref(bad)))
         return int(n.value)
 
+    def payload_timing(self) -> Dict[str, float]:
+        """Device time of the last serialize_payloads' write kernel: {"ms_write", "body_bytes"} (pte_payload_timing)."""
+        a, n = C.c_float(), C.c_uint64()
+        self._ck(self._L.pte_payload_timing(self._h, C.byref(a), C.byref(n)))
+        return {"ms_write": a.value, "body_bytes": int(n.value)}
+
+    def json_timing(self) -> Dict[str, float]:
+        """Device time of the last ingest_json: {"ms_index", "ms_parse", "text_bytes"} (pte_json_timing)."""
+        a, b, n = C.c_float(), C.c_float(), C.c_uint64()
+        self._ck(self._L.pte_json_timing(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return {"ms_index": a.value, "ms_parse": b.value, "text_bytes": int(n.value)}
+
     def json_strings(self, which: int) -> list:
         """Dictionary of the last ingest_json: 0 = namespaces by ns_id, 1 = phase strings for codes 7, 8, ..."""
         n = C.c_uint32()

@@ -1,0 +1,41 @@
+"""Device-side speed of the raw watch-JSON path: line index + scanner kernel, CUDA-event times (no PCIe in them).
+    python tools/json_bench.py [events per block, default 200000] [repeat, default 8]   -> about 1 GB of text"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import fake_kubernetes as fk
+from k8s_watcher_b200 import PhaseTransitionEngine
+from oracle import c_oracle
+ne = int(sys.argv[1]) if len(sys.argv) > 1 else 200_000
+rep = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+cols = c_oracle.generate(0x6B38735F77617463, ne, 3000, dist=1, p_del=0.05, p_nostatus=0.03, p_null=0.03)
+block = fk.watch_json_lines(fk.events_from_columns(cols), seed=1)
+if not block.endswith(b"\n"):
+    block += b"\n"
+text = block * rep
+peak = 6546.9
+with PhaseTransitionEngine(ne * rep + 16, 4000) as e:
+    for _ in range(3):
+        n = e.ingest_json(text)
+        t = e.json_timing()
+    gb = t["text_bytes"] / 1e9
+    print("watch JSON: %d lines, %.3f GB of text (%.0f B/line): line index %.3f ms, scanner kernel %.3f ms = %.0f GB/s of text "
+          "(%.3f of the measured %.1f GB/s HBM peak), %.1f M events/s on the device"
+          % (n, gb, t["text_bytes"] / n, t["ms_index"], t["ms_parse"], gb / (t["ms_parse"] * 1e-3), gb / (t["ms_parse"] * 1e-3) / peak,
+             peak, n / t["ms_parse"] / 1e3))
+
+# request bodies built on the device (pte_serialize_payloads): device time of the kernel that writes them
+import logging; logging.disable(logging.CRITICAL)
+from k8s_watcher_b200 import PodWatcher, ReplayLog
+from k8s_watcher_b200.pod_watcher import payload_fragments
+os.chdir(ROOT)
+w = PodWatcher("staging")
+log = ReplayLog.synthetic(0x6B38735F77617463, 3_000_000, 40_000, p_del=0.05)
+batch = w.replay(log)
+frags, n_phase, n_ns = payload_fragments(w, log, "2025-06-01T12:00:00")
+for _ in range(2):
+    buf, off = w._engine.serialize_payloads(frags, n_phase, n_ns)
+pt = w._engine.payload_timing()
+print("payloads: %d request bodies, %.3f GB: payload_write_kernel %.3f ms = %.0f GB/s written (%.3f of the measured %.1f GB/s HBM peak)"
+      % (len(batch), pt["body_bytes"] / 1e9, pt["ms_write"], pt["body_bytes"] / 1e9 / (pt["ms_write"] * 1e-3),
+         pt["body_bytes"] / 1e9 / (pt["ms_write"] * 1e-3) / peak, peak))
