@@ -341,7 +341,8 @@ def main():
         "intern_pack_kernel": (1, 26.0 * n_in + 8.0 * n_surv + 16.0 * n_surv, avg["ms_intern"]),
         "radix_pass_kernel": (kp, 16.0 * n_surv, pass_ms / pass_n if pass_n else 0.0),
         "diff_flag_kernel": (rounds, 8.0 * n_surv, avg["ms_diff"] / rounds),
-        "assemble_bitmap_kernel": (1, n_in / 8.0 + 14.0 * n_emit + 18.0 * n_emit, avg["ms_assemble"]),
+        # bitmap read + event type gathered + arrival index and type written (rv / ns / phase are on-demand columns now)
+        "assemble_bitmap_kernel": (1, n_in / 8.0 + 1.0 * n_emit + 5.0 * n_emit, avg["ms_assemble"]),
     }
     by_kernel = {}
     for name, (per_step, nbytes, ms) in per_kernel.items():

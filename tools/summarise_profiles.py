@@ -1,6 +1,6 @@
 """gpurun_out/{launches.csv, prof_full.ncu-rep, plain.log} -> profiles/<tag>/ (tracked summaries) + profiles/traffic.json."""
 import collections, csv, json, os, shutil, subprocess, sys
-tag = sys.argv[1] if len(sys.argv) > 1 else "r01_final"
+tag = sys.argv[1] if len(sys.argv) > 1 else "r02_final"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 src, dst = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles", tag)
 os.makedirs(dst, exist_ok=True)
