@@ -27,6 +27,14 @@
 #pragma once
 #include "pte_kernels.cuh"
 
+// Measured on B200, 1 B events (profiles/r02_partition): ballots + word-by-word write-out 18.2 ms; MATCH.ANY ranking 20.9 ms
+// (the ADU pipe serialises it); one lane per record in the write-out 22.5 ms (three times the L2 write transactions); both 24.9 ms.
+#ifndef PTE_SCATTER_WORDWISE
+#define PTE_SCATTER_WORDWISE 1
+#endif
+#ifndef PTE_SCATTER_MATCH
+#define PTE_SCATTER_MATCH 0
+#endif
 static constexpr int kPartBits = 10;
 static constexpr int kParts = 1 << kPartBits;
 static constexpr u64 kPartSalt = 0x7061727469746E21ull;
@@ -34,7 +42,19 @@ static constexpr u32 kMinSegment = 1u << 15;          // records; shorter partit
 static constexpr u32 kMaxSegments = 16 * kParts;
 static constexpr u32 kSampleSegments = 4;             // extra entries behind the segment table: the polarity sample
 
-__host__ __device__ __forceinline__ u32 part_of(u64 uid_lo) { return (u32)(mix64(uid_lo ^ kPartSalt) >> (64 - kPartBits)); }
+// partition of a uid: one xor-shift and one multiply of uid_lo (the counting pass reads that column only)
+__host__ __device__ __forceinline__ u32 part_of(u64 uid_lo) {
+    u64 x = uid_lo ^ kPartSalt;
+    x ^= x >> 32;
+    return (u32)((x * 0x9E3779B97F4A7C15ull) >> (64 - kPartBits));
+}
+// 24 more hash bits, of both halves, computed once by the scatter and carried in bits [38, 62) of the record's third word:
+// the replay takes the uid's home line and its 8-bit fingerprint from them
+__host__ __device__ __forceinline__ u32 uid_hash24(u64 hi, u64 lo) {
+    u64 x = lo ^ (hi * 0xD1B54A32D192ED03ull);
+    x ^= x >> 29;
+    return (u32)((x * 0xBF58476D1CE4E5B9ull) >> 40);
+}
 
 struct __align__(16) Segment {
     u32 beg, end;          // records [beg, end) of the partition-ordered buffer
@@ -250,6 +270,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) part_scatter_kernel(Scatt
             bool valid = j < tile_valid;
             if (FILTERED) valid = valid && ((keepw[k] >> lane) & 1u);
             const u32 b = part_of(lo[k]);
+            // lanes of this step that go to the same partition
+#if PTE_SCATTER_MATCH
+            u32 peers = __match_any_sync(0xffffffffu, valid ? b : 0xFFFF0000u | lane);
+#else
             u32 peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
             for (int q = 0; q < kPartBits; q++) {
@@ -257,6 +281,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) part_scatter_kernel(Scatt
                 const u32 m = __ballot_sync(0xffffffffu, bit);
                 peers &= bit ? m : ~m;
             }
+#endif
             if (!valid) peers = 0;
             const u32 before = peers & lt;
             u32 wbase = 0;
@@ -316,7 +341,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) part_scatter_kernel(Scatt
                 del_surv += ty == kTypeDeleted;
                 s.stage[pos * 3] = hi[k];
                 s.stage[pos * 3 + 1] = lo[k];
-                s.stage[pos * 3 + 2] = ((tile_base + j) << 8) | ((u64)(ty & 3u) << 6) | (eff_phase(ph) & 63u);
+                s.stage[pos * 3 + 2] = ((u64)uid_hash24(hi[k], lo[k]) << 38) | ((tile_base + j) << 8) | ((u64)(ty & 3u) << 6) | (eff_phase(ph) & 63u);
                 s.sbin[pos] = (unsigned short)b;
             }
         }
@@ -356,12 +381,23 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) part_scatter_kernel(Scatt
         }
         __syncthreads();
 
-        // (6) runs out to global memory, word by word: a (tile, partition) run leaves as one contiguous piece
+        // (6) runs out to global memory: a (tile, partition) run leaves as one contiguous piece
+#if PTE_SCATTER_WORDWISE
 #pragma unroll 4
         for (u32 w = tid; w < survivors * 3; w += THREADS) {
             const u32 rec = w / 3;
             __stcs(a.out + (u64)(s.dst_off[s.sbin[rec]] + rec) * 3 + (w - rec * 3), s.stage[w]);
         }
+#else
+        // a lane per record (three 8-byte stores 24 bytes apart; neighbouring lanes fill the gaps, L2 merges the sectors):
+        // a third of the index arithmetic of the word-by-word form
+#pragma unroll 2
+        for (u32 rec = tid; rec < survivors; rec += THREADS) {
+            u64* d = a.out + (u64)(s.dst_off[s.sbin[rec]] + rec) * 3;
+            const u64 w0 = s.stage[rec * 3], w1 = s.stage[rec * 3 + 1], w2 = s.stage[rec * 3 + 2];
+            __stcs(d, w0); __stcs(d + 1, w1); __stcs(d + 2, w2);
+        }
+#endif
         tile = next_tile;
         __syncthreads();
     }
@@ -410,11 +446,18 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity, u32 sleep_ns) {
 // truth: a stale 0 tag (another CTA replaying a different segment of the same partition filled the slot) makes
 // the 128-bit CAS fail, which returns the slot's content and repairs the tag.
 struct UidHash { u32 line, fp; };
-__device__ __forceinline__ UidHash uid_hash(u64 hi, u64 lo, u32 line_mask) {
-    const u64 h = mix64(hi ^ (lo * 0x9E3779B97F4A7C15ull));
+__device__ __forceinline__ UidHash uid_hash_of_bits(u32 h, u32 line_mask) {
     UidHash r;
-    r.line = (u32)h & line_mask;
-    r.fp = (u32)(h >> 56);
+    r.line = h & line_mask;
+    r.fp = h >> 16;
+    r.fp += r.fp == 0;
+    return r;
+}
+__device__ __forceinline__ UidHash uid_hash(u64 hi, u64 lo, u32 line_mask) {
+    const u32 h = uid_hash24(hi, lo);
+    UidHash r;
+    r.line = h & line_mask;            // at most 13 bits (slices of up to 65536 slots)
+    r.fp = h >> 16;
     r.fp += r.fp == 0;
     return r;
 }
@@ -519,7 +562,7 @@ __device__ __forceinline__ void replay_event(ReplayCtx& c, u32 pred, u64 meta, u
     } else {
         const bool e = emits(pred, tp);
         c.n_emit += e; c.n_seen++;
-        if (!a.count_only && e != c.invert) flip_bit(a.bitmap, (u32)(meta >> 8));
+        if (!a.count_only && e != c.invert) flip_bit(a.bitmap, (u32)(meta >> 8) & 0x3FFFFFFFu);
     }
 }
 
@@ -626,7 +669,7 @@ __global__ void __launch_bounds__(kRpThreads, 1) part_replay_kernel(ReplayArgs a
                     r[k] = pw * kRpWarpRecs + k * 32 + lane;
                     ok[k] = r[k] < valid;
                     hi[k] = ok[k] ? tb[r[k] * 3] : 0; lo[k] = ok[k] ? tb[r[k] * 3 + 1] : 0;
-                    const UidHash uh = uid_hash(hi[k], lo[k], line_mask);
+                    const UidHash uh = uid_hash_of_bits(ok[k] ? (u32)(tb[r[k] * 3 + 2] >> 38) & 0xFFFFFFu : 0u, line_mask);
                     line[k] = uh.line;
                     cm[k] = ok[k] ? tag_masks(uh.line, uh.fp) : 0u;
                     slot_of[k] = 0;
@@ -816,7 +859,7 @@ pending_fixup_kernel(const PendingHead* __restrict__ pending, u32 pending_cap, c
             const u32 st = seg_export[(u64)(p.seg - back) * slice_slots + p.slot];
             if (st != 0xFFu) { pred = st; break; }
         }
-        if (emits(pred, (u32)p.meta & 0xFFu) != invert) flip_bit(bitmap, (u32)(p.meta >> 8));
+        if (emits(pred, (u32)p.meta & 0xFFu) != invert) flip_bit(bitmap, (u32)(p.meta >> 8) & 0x3FFFFFFFu);
     }
 }
 
