@@ -202,7 +202,10 @@ int pte_fetch_bitmap(pte_handle h, uint32_t* words, uint64_t cap_words, uint64_t
  * notifications as pte_ingest + pte_run on the whole log (dedupe as in pte_run); the emit bitmap lands in
  * bitmap_out ((n + 31) / 32 words, layout of pte_fetch_bitmap), the counts in *out (times are sums over chunks).
  * This is the payload hand-off of pod_watcher.py:232-236 for a host that holds the log.  The log must be in
- * resourceVersion order (PTE_ERR_UNORDERED otherwise); ns_id may be NULL as in pte_ingest.  The log stays resident. */
+ * resourceVersion order (PTE_ERR_UNORDERED otherwise); ns_id may be NULL as in pte_ingest.  rv may be NULL too: the
+ * caller then vouches that the log is in arrival order -- the only order the reference's loop knows, it never reads
+ * metadata.resourceVersion -- and the position serves as order key (8 of the 26 bytes per event stay at home).
+ * The log stays resident. */
 int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
                          const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n,
                          uint64_t chunk_events, int dedupe, uint32_t* bitmap_out, pte_stats* out);

@@ -1087,7 +1087,7 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
                          uint32_t* bitmap_out, pte_stats* out) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
-    if (n && (!uid_hi || !uid_lo || !rv || !phase || !type || !bitmap_out)) FAIL(h, PTE_ERR_INVALID, "NULL column or bitmap");
+    if (n && (!uid_hi || !uid_lo || !phase || !type || !bitmap_out)) FAIL(h, PTE_ERR_INVALID, "NULL column or bitmap");
     if (n && !ns_id && h->ns_filter_on) FAIL(h, PTE_ERR_INVALID, "ns_id may only be NULL while no namespace allow-list is set");
     CK(h, cudaSetDevice(h->device));
     if (!h->copy_stream) CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -1106,7 +1106,7 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
         const u64 off = k * chunk_events, len = std::min<u64>(chunk_events, n - off);
         CK(h, cudaMemcpyAsync(h->uid_hi + off, uid_hi + off, len * 8, cudaMemcpyHostToDevice, cs));
         CK(h, cudaMemcpyAsync(h->uid_lo + off, uid_lo + off, len * 8, cudaMemcpyHostToDevice, cs));
-        CK(h, cudaMemcpyAsync(h->rv + off, rv + off, len * 8, cudaMemcpyHostToDevice, cs));
+        if (rv) CK(h, cudaMemcpyAsync(h->rv + off, rv + off, len * 8, cudaMemcpyHostToDevice, cs));
         if (ns_id) CK(h, cudaMemcpyAsync(h->ns + off, ns_id + off, len * 4, cudaMemcpyHostToDevice, cs));
         CK(h, cudaMemcpyAsync(h->phase + off, phase + off, len, cudaMemcpyHostToDevice, cs));
         CK(h, cudaMemcpyAsync(h->type + off, type + off, len, cudaMemcpyHostToDevice, cs));
@@ -1126,8 +1126,14 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
         h->uid_hi = sv.uid_hi + off; h->uid_lo = sv.uid_lo + off; h->rv = sv.rv + off; h->ns = sv.ns + off;
         h->phase = sv.phase + off; h->type = sv.type + off; h->bitmap = sv.bitmap + off / 32; h->keepmap = sv.keepmap + off / 32;
         h->n_events = len;
-        h->batch_first_rv = rv[off]; h->batch_last_rv = rv[off + len - 1];
-        if (!dedupe && k > 0 && rv[off] < rv[off - 1]) { h->err = "resourceVersion decreases between two chunks"; rc = PTE_ERR_UNORDERED; break; }
+        if (rv) {
+            h->batch_first_rv = rv[off]; h->batch_last_rv = rv[off + len - 1];
+            if (!dedupe && k > 0 && rv[off] < rv[off - 1]) { h->err = "resourceVersion decreases between two chunks"; rc = PTE_ERR_UNORDERED; break; }
+        } else {
+            // the caller vouches for arrival order: the order key is the position (the reference's loop has no other)
+            iota_rv_kernel<<<(int)std::min<u64>((len + 255) / 256, (u64)h->num_sms * 8), 256, 0, h->stream>>>(h->rv, len, off + 1);
+            h->batch_first_rv = off + 1; h->batch_last_rv = off + len;
+        }
         pte_stats st;
         h->in_reorder = true;                                   // an unordered chunk is an error here, not a reason to pre-sort
         rc = pte_run(h, flags, &st);

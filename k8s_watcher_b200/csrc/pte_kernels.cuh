@@ -661,6 +661,11 @@ __global__ void __launch_bounds__(256, PTE_ASM_BLOCKS) assemble_bitmap_kernel(As
     }
 }
 
+// Order keys for a log that is declared to be in arrival order (pte_replay_pipelined with rv == NULL): 1, 2, 3, ...
+__global__ void __launch_bounds__(256) iota_rv_kernel(u64* __restrict__ rv, u64 n, u64 first) {
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) rv[i] = first + i;
+}
+
 // rv, namespace and phase of the emitted records, on demand (pte_fetch of those columns, payload serialisation)
 __global__ void __launch_bounds__(256)
 emitted_columns_kernel(const u32* __restrict__ out_idx, u64 n, const u64* __restrict__ rv, const u32* __restrict__ ns,

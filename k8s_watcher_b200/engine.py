@@ -279,7 +279,7 @@ class PhaseTransitionEngine:
         return out[:words]
 
     def replay_pipelined(self, cols: Dict[str, np.ndarray], *, dedupe: bool = True, chunk_events: int = 0,
-                         with_namespaces: bool = True, bitmap_out: Optional[np.ndarray] = None):
+                         with_namespaces: bool = True, with_rv: bool = True, bitmap_out: Optional[np.ndarray] = None):
         """ingest + run + fetch_bitmap as one pipelined call (pte_replay_pipelined): host -> device copies of later
         chunks overlap the replay of earlier ones.  Columns in pinned memory (PinnedBuffer) copy at full PCIe speed.
         Returns (emit bitmap words, stats)."""
@@ -289,7 +289,8 @@ class PhaseTransitionEngine:
         out = bitmap_out if bitmap_out is not None else np.zeros(max(words, 1), np.uint32)
         st = PteStats()
         self._ck(self._L.pte_replay_pipelined(
-            self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64), _ptr(c["rv"], C.c_uint64),
+            self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64),
+            _ptr(c["rv"], C.c_uint64) if with_rv else None,      # with_rv=False: the caller vouches for arrival order
             _ptr(c["ns_id"], C.c_uint32) if with_namespaces else None, _ptr(c["phase"], C.c_uint8),
             _ptr(c["type"], C.c_uint8), n, int(chunk_events), int(bool(dedupe)), _ptr(out, C.c_uint32), C.byref(st)))
         self.last_stats = st.as_dict()

@@ -341,6 +341,7 @@ class PodWatcher:
             # home when no allow-list could look at it
             try:
                 bitmap, stats = eng.replay_pipelined(log.columns, dedupe=dedupe, with_namespaces=bool(names),
+                                                     with_rv=not log.arrival_ordered,
                                                      chunk_events=self.pipeline_chunk_events,
                                                      bitmap_out=log.bitmap_buffer())
                 batch = Batch(self, log, None, stats, dedupe, bitmap=bitmap)

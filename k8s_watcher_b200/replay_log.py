@@ -27,6 +27,9 @@ class ReplayLog:
         # code -> phase string; codes 0..6 are fixed by include/pte.h
         self.phases = list(phases) if phases else list(codes.PHASE_NAMES) + [None, None]
         self._pods = pods            # per-row pod objects when the log came from a live stream
+        # True: the rows are in the order the watcher received them and that IS the replay order (the reference's loop
+        # knows no other; it never reads resourceVersion).  replay() then leaves the rv column on the host.
+        self.arrival_ordered = False
 
     def __len__(self):
         return int(self.columns["rv"].shape[0])
@@ -104,7 +107,9 @@ class ReplayLog:
         for k, v in ns_ids.items():
             names[v] = k
         shared[:] = names
-        return cls(cols, names, phases, pods)
+        log = cls(cols, names, phases, pods)
+        log.arrival_ordered = seq_start is not None
+        return log
 
     @classmethod
     def from_watch_json(cls, engine, text: bytes) -> "ReplayLog":

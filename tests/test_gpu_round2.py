@@ -352,3 +352,15 @@ def test_podwatcher_replay_pipelines_long_logs(monkeypatch):
             assert b2.bitmap is None and np.array_equal(b2.indices.astype(np.uint64), want2)
     finally:
         log.free()
+
+
+def test_pipelined_replay_without_rv_column_for_arrival_ordered_logs():
+    """A log declared to be in arrival order needs no resourceVersion column on the device: positions are the order."""
+    n, pods = 150_001, 2_000
+    cols = c_oracle.generate(SEED + 12, n, pods, dist=1, p_del=0.06)
+    want, ost, _ = c_oracle.replay(cols, pods_hint=pods)
+    junk = dict(cols, rv=np.zeros(n, np.uint64))                   # must not be looked at
+    with PhaseTransitionEngine(n, pods) as e:
+        words, st = e.replay_pipelined(junk, chunk_events=32_768, with_namespaces=False, with_rv=False)
+        bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n]
+        assert np.array_equal(np.flatnonzero(bits).astype(np.uint64), want) and st["n_emitted"] == ost["n_emitted"]
