@@ -1275,7 +1275,6 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
         CK(h, cudaMalloc((void**)&h->json_ph_keys, kJsonPhSlots * sizeof(u64)));
         CK(h, cudaMalloc((void**)&h->json_ph_off, kJsonPhSlots * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_err, 4 * sizeof(u32)));
-        CK(h, cudaFuncSetAttribute(json_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kJsonWarps * (kJsonWindow + 16)));
         CK(h, cudaMalloc((void**)&h->json_ns_remap, kJsonNsSlots * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_ph_remap, kJsonPhSlots));
     }
@@ -1291,9 +1290,9 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     a.ns_dict = StrDict{h->json_ns_keys, h->json_ns_off, kJsonNsSlots - 1};
     a.phase_dict = StrDict{h->json_ph_keys, h->json_ph_off, kJsonPhSlots - 1};
     a.err = h->json_err;
-    grid = (int)std::min<u64>((n_lines + 127) / 128, (u64)h->num_sms * 2);
+    grid = (int)std::min<u64>((n_lines + kJsonThreads - 1) / kJsonThreads, (u64)h->num_sms * 8);
     CK(h, cudaEventRecord(h->ev[1], st));
-    json_parse_kernel<<<grid, kJsonWarps * 32, kJsonWarps * (kJsonWindow + 16), st>>>(a, h->json_err + 2);
+    json_parse_kernel<<<grid, kJsonThreads, 0, st>>>(a, h->json_err + 2);
     CK(h, cudaGetLastError());
     CK(h, cudaEventRecord(h->ev[2], st));
     u32 err[2];

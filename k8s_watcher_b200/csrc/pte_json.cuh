@@ -11,119 +11,30 @@
 // string dictionary: candidates are compared byte by byte against the first occurrence.
 #pragma once
 #include "pte_common.cuh"
+#include "pte_json_scan.h"
 
 enum : u32 { kJsonOk = 0, kJsonMalformed = 1, kJsonBadType = 2, kJsonBadUid = 3, kJsonBadRv = 4, kJsonEscapedField = 5,
              kJsonDictFull = 6, kJsonTooManyPhases = 7 };
 
-struct JsonSpan { u64 s; u32 len; bool present, escaped; };
+// ---- the scanner: pte_json_scan.h (plain C++, shared with the CPU test harness) ----------------------------
+typedef ptejson::Span JsonSpan;
+typedef ptejson::Fields JsonFields;
 
-// ---- the scanner ---------------------------------------------------------------------------------------
-// One pass over the bytes of a line with a handful of state variables, the same few instructions for every byte:
-// threads of a warp scan 32 different lines, and a recursive-descent scanner (one code path per syntactic
-// situation) had them take turns -- 300 k warp instructions per 32 lines, measured.  State: nesting depth, a bit
-// per depth saying "object or array", the meaning of the containers at depths 1..3 (root / object / metadata /
-// status / other), whether a string is a key, and which field the value after the last key is for.
-struct JsonFields { JsonSpan type, uid, ns, rv, phase; bool has_status; };
-
-__host__ __device__ constexpr u32 json_fnv(const char* s, u32 n) {
-    u32 h = 2166136261u;
-    for (u32 i = 0; i < n; i++) h = (h ^ (u32)(unsigned char)s[i]) * 16777619u;
-    return h;
-}
-template <typename T>
-__device__ __forceinline__ bool json_bytes_are(const T& t, u64 s, const char* name, u32 n) {
-    for (u32 i = 0; i < n; i++) if (t[s + i] != name[i]) return false;
-    return true;
-}
-
-template <typename T>
-__device__ __forceinline__ bool json_scan_line(const T& t, u64 p, u64 end, JsonFields& f) {
-    enum : u32 { C_OTHER = 0, C_ROOT = 1, C_OBJECT = 2, C_META = 3, C_STATUS = 4 };
-    enum : u32 { W_NONE = 0, W_TYPE = 1, W_UID = 2, W_NS = 3, W_RV = 4, W_PHASE = 5, W_OBJECT = 6, W_META = 7, W_STATUS = 8 };
-    const JsonSpan none = {0, 0, false, false};
-    f.type = f.uid = f.ns = f.rv = f.phase = none;
-    f.has_status = false;
-    u32 depth = 0, ctxs = 0, want = W_NONE, h = 0;
-    u64 is_obj = 0, str_start = 0;
-    bool in_str = false, esc = false, str_esc = false, is_key = false, expect_key = false, bad = false, opened = false;
-    u32 key_h = 0, key_len = 0;
-    u64 key_s = 0;
-    bool key_ok = false;
-    for (; p < end; p++) {
-        const char c = t[p];
-        if (in_str) {
-            if (esc) esc = false;
-            else if (c == '\\') { esc = true; str_esc = true; }
-            else if (c == '"') {
-                in_str = false;
-                if (is_key) { key_h = h; key_len = (u32)(p - str_start); key_s = str_start; key_ok = !str_esc; }
-                else {
-                    if (want >= W_TYPE && want <= W_PHASE) {
-                        const JsonSpan sp = {str_start, (u32)(p - str_start), true, str_esc};
-                        if (want == W_TYPE) f.type = sp; else if (want == W_UID) f.uid = sp; else if (want == W_NS) f.ns = sp;
-                        else if (want == W_RV) f.rv = sp; else f.phase = sp;
-                    }
-                    want = W_NONE;
-                }
-            } else h = (h ^ (u32)(unsigned char)c) * 16777619u;
-            continue;
-        }
-        if (c == ' ' || c == '\t' || c == '\r' || c == '\n') continue;
-        if (c == '"') {
-            in_str = true; str_esc = false; h = 2166136261u; str_start = p + 1;
-            is_key = expect_key; expect_key = false;
-        } else if (c == ':') {
-            // the key just read decides what the value is for
-            const u32 ctx = depth <= 7 ? (ctxs >> (4 * depth)) & 15u : C_OTHER;
-            want = W_NONE;
-            if (key_ok && ctx != C_OTHER) {
-                u32 w = W_NONE; const char* name = ""; u32 n = 0;
-                if (ctx == C_ROOT) {
-                    if (key_len == 4 && key_h == json_fnv("type", 4)) { w = W_TYPE; name = "type"; n = 4; }
-                    else if (key_len == 6 && key_h == json_fnv("object", 6)) { w = W_OBJECT; name = "object"; n = 6; }
-                } else if (ctx == C_OBJECT) {
-                    if (key_len == 8 && key_h == json_fnv("metadata", 8)) { w = W_META; name = "metadata"; n = 8; }
-                    else if (key_len == 6 && key_h == json_fnv("status", 6)) { w = W_STATUS; name = "status"; n = 6; }
-                } else if (ctx == C_META) {
-                    if (key_len == 3 && key_h == json_fnv("uid", 3)) { w = W_UID; name = "uid"; n = 3; }
-                    else if (key_len == 9 && key_h == json_fnv("namespace", 9)) { w = W_NS; name = "namespace"; n = 9; }
-                    else if (key_len == 15 && key_h == json_fnv("resourceVersion", 15)) { w = W_RV; name = "resourceVersion"; n = 15; }
-                } else if (ctx == C_STATUS) {
-                    if (key_len == 5 && key_h == json_fnv("phase", 5)) { w = W_PHASE; name = "phase"; n = 5; }
-                }
-                if (w != W_NONE && json_bytes_are(t, key_s, name, n)) {      // the hash only nominates, the bytes decide
-                    want = w;
-                    // a value that is not a string (null, a number) leaves the field absent; a later duplicate key wins
-                    if (w == W_TYPE) f.type = none; else if (w == W_UID) f.uid = none; else if (w == W_NS) f.ns = none;
-                    else if (w == W_RV) f.rv = none; else if (w == W_PHASE) f.phase = none;
-                }
-            }
-        } else if (c == '{' || c == '[') {
-            u32 nc = C_OTHER;
-            if (c == '{') {
-                if (depth == 0) nc = C_ROOT;
-                else if (want == W_OBJECT) nc = C_OBJECT;
-                else if (want == W_META) nc = C_META;
-                else if (want == W_STATUS) { nc = C_STATUS; f.has_status = true; }      // pod.status is truthy (pod_watcher.py:167,209)
-            }
-            opened = true;
-            depth++;
-            if (depth <= 7) ctxs = (ctxs & ~(15u << (4 * depth))) | (nc << (4 * depth));
-            if (depth < 64) is_obj = c == '{' ? is_obj | (1ull << depth) : is_obj & ~(1ull << depth);
-            expect_key = c == '{';
-            want = W_NONE; key_ok = false;
-        } else if (c == '}' || c == ']') {
-            if (depth == 0) bad = true; else depth--;
-            expect_key = false; want = W_NONE; key_ok = false;
-        } else if (c == ',') {
-            expect_key = depth < 64 && ((is_obj >> depth) & 1ull);
-            want = W_NONE; key_ok = false;
-        } else {
-            if (!opened) bad = true;          // a line must start with '{'
-            want = W_NONE;                    // a literal or a number: not a string value
-        }
+// the text in global memory: bytes by offset, 32-byte blocks by aligned offset (two 16-byte loads)
+struct GlobalText {
+    const char* base;
+    __device__ __forceinline__ char operator[](u64 i) const { return base[i]; }
+    __device__ __forceinline__ void load32(u64 blk, u32 (&w)[8]) const {
+        const uint4* g = reinterpret_cast<const uint4*>(base + blk);
+        const uint4 a = __ldg(g), b = __ldg(g + 1);
+        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     }
-    return opened && depth == 0 && !in_str && !bad;
+};
+template <typename T>
+__device__ __forceinline__ bool span_has_backslash(const T& t, const JsonSpan& sp) {
+    bool any = false;
+    for (u32 k = 0; sp.present && k < sp.len; k++) any = any || t[sp.s + k] == '\\';
+    return any;
 }
 
 // ---- exact string dictionary -----------------------------------------------------------------------
@@ -230,8 +141,9 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
         JsonFields f;
         u64 hi = 0, lo = 0, rv = i + 1;
         u32 type = 0, phase = kPhNoStatus, ns = 0;
-        if (!json_scan_line(t, p, end, f)) bad = kJsonMalformed;
-        if (!bad && (f.type.escaped || f.uid.escaped || f.ns.escaped || f.rv.escaped || f.phase.escaped)) bad = kJsonEscapedField;
+        if (!ptejson::scan_line(t, p, end, f)) bad = kJsonMalformed;
+        if (!bad && (span_has_backslash(t, f.type) || span_has_backslash(t, f.uid) || span_has_backslash(t, f.ns) ||
+                     span_has_backslash(t, f.rv) || span_has_backslash(t, f.phase))) bad = kJsonEscapedField;
         if (!bad) {
             // event['type'] (pod_watcher.py:267): ADDED / MODIFIED / DELETED, anything else is rejected
             const char c0 = f.type.present && f.type.len ? t[f.type.s] : 0;
@@ -286,58 +198,27 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
     }
 }
 
-// A window of the text held in shared memory, addressed by offsets in the text.
-struct SmemText {
-    const char* base; u64 off;
-    __device__ __forceinline__ char operator[](u64 i) const { return base[i - off]; }
-};
+// One thread per line, 32 consecutive lines per warp (handed out by ticket, so long and short lines even out); the
+// text comes straight from global memory in 32-byte blocks, the next block in flight while the current one is scanned.
+static constexpr int kJsonThreads = 128;
 
-// Lines are a few hundred bytes of text each and a thread scans its line byte by byte: straight from global
-// memory that is one sector per lane and step.  So a warp first copies the text of its next lines (they are
-// consecutive in the log, hence one contiguous range) into shared memory with coalesced 16-byte loads, and every
-// lane then scans its line there.  A line longer than the warp's window is scanned in place.
-static constexpr int kJsonWarps = 4, kJsonWindow = 27 * 1024;      // bytes of text per warp and round (two blocks per SM)
-
-__global__ void __launch_bounds__(kJsonWarps * 32) json_parse_kernel(JsonArgs a, u32* __restrict__ ticket) {
-    extern __shared__ __align__(16) char s_text[];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    char* win = s_text + warp * (kJsonWindow + 16);
+__global__ void __launch_bounds__(kJsonThreads) json_parse_kernel(JsonArgs a, u32* __restrict__ ticket) {
+    const u32 lane = threadIdx.x & 31;
+    const GlobalText t{a.text};
     for (;;) {
         u64 g0 = 0;
         if (lane == 0) g0 = (u64)atomicAdd(ticket, 1u) * 32;
         g0 = __shfl_sync(0xffffffffu, g0, 0);
         if (g0 >= a.n_lines) break;
-        const u64 g1 = min(a.n_lines, g0 + 32);
-        u64 s = g0;
-        while (s < g1) {
-            // as many of the remaining lines of the group as fit into the window
-            const u64 beg = s ? a.nl[s - 1] + 1 : 0;
-            const u64 li = s + lane;
-            const u64 my_end = li < g1 ? (li < a.n_nl ? a.nl[li] : a.len) : 0;
-            const u32 fits = __ballot_sync(0xffffffffu, li < g1 && my_end - beg <= (u64)kJsonWindow);
-            const u32 c = fits == 0xFFFFFFFFu ? 32u : (u32)__ffs(~fits) - 1;     // lines s .. s+c-1 fit (fits is a prefix of ones)
-            if (c == 0) {
-                if (lane == 0) json_line(a, a.text, s, beg, my_end);      // one very long line: scanned in place
-                s += 1;
-                __syncwarp();
-                continue;
-            }
-            const u64 end_all = __shfl_sync(0xffffffffu, my_end, c - 1);
-            const u64 abeg = beg & ~15ull;               // the text buffer is 256-byte aligned and padded
-            for (u64 o = abeg + lane * 16; o < end_all; o += 512)
-                *reinterpret_cast<uint4*>(win + (o - abeg)) = __ldcs(reinterpret_cast<const uint4*>(a.text + o));
-            __syncwarp();
-            if (lane < c) {
-                const u64 p = li ? a.nl[li - 1] + 1 : 0;
-                json_line(a, SmemText{win, abeg}, li, p, my_end);
-            }
-            __syncwarp();
-            s += c;
+        const u64 li = g0 + lane;
+        if (li < a.n_lines) {
+            const u64 p = li ? a.nl[li - 1] + 1 : 0;
+            const u64 end = li < a.n_nl ? a.nl[li] : a.len;
+            json_line(a, t, li, p, end);
         }
+        __syncwarp();
     }
 }
-
-
 
 // dictionary slots -> dense ids in order of first occurrence (remap tables built by the host)
 __global__ void __launch_bounds__(256)
