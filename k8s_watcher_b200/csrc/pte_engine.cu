@@ -1237,6 +1237,8 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
 
 static constexpr u32 kJsonNsSlots = 1u << 16, kJsonPhSlots = 128;
 
+struct HostJsonText { const char* base; __host__ __device__ char operator[](u32 i) const { return base[i]; } };
+
 int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line) {
     if (!h || (!text && len)) FAIL(h, PTE_ERR_INVALID, "NULL argument");
     if (n_events) *n_events = 0;
@@ -1250,6 +1252,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     int rc;
     if ((rc = grow(h, &h->json_text, &h->json_text_cap, len + 64))) return rc;
     CK(h, cudaMemcpyAsync(h->json_text, text, len, cudaMemcpyHostToDevice, st));
+    CK(h, cudaMemsetAsync(h->json_text + len, 0, 64, st));                    // the kernels read whole 16- and 32-byte blocks
     // 1. line index
     const u64 chunks = (len + kJsonChunk - 1) / kJsonChunk;
     if ((rc = grow(h, &h->json_chunk_cnt, &h->json_chunk_cap, chunks))) return rc;
@@ -1306,7 +1309,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaStreamSynchronize(st));
     if (err[0]) {
         static const char* why[] = {"", "malformed JSON", "event type is not ADDED/MODIFIED/DELETED", "metadata.uid is not a 128-bit hex uid",
-                                    "metadata.resourceVersion is not a decimal number", "a field the path reads contains an escape sequence",
+                                    "metadata.resourceVersion is not a decimal number", "a field the path reads contains a broken escape sequence",
                                     "more distinct namespaces than the device dictionary holds", "too many distinct phase strings"};
         if (bad_line) *bad_line = err[1];
         h->n_events = 0;
@@ -1320,7 +1323,11 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
         remap.assign(keys.size(), 0);
         for (u32 id = 0; id < occ.size(); id++) {
             const u32 sl = occ[id].second, l = (u32)(keys[sl] & 0xFFFFFu);
-            names.emplace_back(text + occ[id].first, l);
+            std::string name;                     // l DECODED bytes: the first occurrence may be spelled with escapes
+            const HostJsonText ht{text};
+            ptejson::Unescape<HostJsonText> u(ht, occ[id].first);
+            for (u32 k = 0; k < l; k++) name.push_back((char)u.next());
+            names.push_back(std::move(name));
             remap[sl] = id;
         }
     };

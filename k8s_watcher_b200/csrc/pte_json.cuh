@@ -20,20 +20,31 @@ enum : u32 { kJsonOk = 0, kJsonMalformed = 1, kJsonBadType = 2, kJsonBadUid = 3,
 typedef ptejson::Span JsonSpan;
 typedef ptejson::Fields JsonFields;
 
-// the text in global memory: bytes by offset, 32-byte blocks by aligned offset (two 16-byte loads)
+// the text in global memory: bytes by offset, 32-byte blocks by aligned offset (two 16-byte loads), eight bytes from any offset
 struct GlobalText {
     const char* base;
-    __device__ __forceinline__ char operator[](u64 i) const { return base[i]; }
-    __device__ __forceinline__ void load32(u64 blk, u32 (&w)[8]) const {
+    __device__ __forceinline__ char operator[](u32 i) const { return base[i]; }
+    __device__ __forceinline__ void load32(u32 blk, u32 (&w)[8]) const {
         const uint4* g = reinterpret_cast<const uint4*>(base + blk);
         const uint4 a = __ldg(g), b = __ldg(g + 1);
         w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     }
+    __device__ __forceinline__ u64 load8(u32 s) const {
+        const u64* g = reinterpret_cast<const u64*>(base + (s & ~7u));
+        const u64 a = __ldg(g), b = __ldg(g + 1);
+        const u32 sh = (s & 7u) * 8u;
+        return sh ? (a >> sh) | (b << (64u - sh)) : a;
+    }
+};
+// a few decoded bytes in local memory, for the rare field that is spelled with escapes
+struct LocalText {
+    const char* base;
+    __device__ __forceinline__ char operator[](u32 i) const { return base[i]; }
 };
 template <typename T>
-__device__ __forceinline__ bool span_has_backslash(const T& t, const JsonSpan& sp) {
+__device__ __forceinline__ bool has_backslash(const T& t, u32 s, u32 len) {
     bool any = false;
-    for (u32 k = 0; sp.present && k < sp.len; k++) any = any || t[sp.s + k] == '\\';
+    for (u32 k = 0; k < len; k++) any = any || t[s + k] == '\\';
     return any;
 }
 
@@ -44,12 +55,21 @@ __device__ __forceinline__ bool span_has_backslash(const T& t, const JsonSpan& s
 struct StrDict { u64* keys; u32* first_off; u32 mask; };
 static constexpr u32 kNoOffset = 0xFFFFFFFFu;
 
-// t: where the candidate's bytes are read from (global text or a shared-memory window of it); g: the global text,
-// against which earlier occurrences are compared.  s is the candidate's offset in the global text.
+// [s, s + raw_len) is the candidate's string body in the text.  Strings are the same when the bytes they STAND FOR are
+// the same: "ab" and "a\u0062" share a slot.  The hash and the stored length are those of the decoded bytes; the common
+// case (no backslash on either side) never decodes anything.
 template <typename T>
-__device__ __forceinline__ u32 dict_intern(const StrDict& d, const char* g, const T& t, u64 s, u32 len, u32* err) {
+__device__ __forceinline__ u32 dict_intern(const StrDict& d, const T& t, u32 s, u32 raw_len, u32& bad) {
     u64 h = 0xCBF29CE484222325ull;
-    for (u32 i = 0; i < len; i++) h = (h ^ (u8)t[s + i]) * 0x100000001B3ull;
+    bool esc = false;
+    for (u32 i = 0; i < raw_len; i++) { const char c = t[s + i]; esc = esc || c == '\\'; h = (h ^ (u8)c) * 0x100000001B3ull; }
+    u32 len = raw_len;
+    if (esc) {
+        ptejson::Unescape<T> u(t, s);
+        h = 0xCBF29CE484222325ull; len = 0;
+        while ((u.pos < s + raw_len || u.n_queue) && !u.bad) { h = (h ^ u.next()) * 0x100000001B3ull; len++; }
+        if (u.bad || u.pos > s + raw_len) { bad = kJsonEscapedField; return 0; }
+    }
     h = mix64(h);
     const u64 key = (h & ~0xFFFFFull) | (len & 0xFFFFFu) | (1ull << 63);
     u32 slot = (u32)(h >> 24) & d.mask;
@@ -57,34 +77,44 @@ __device__ __forceinline__ u32 dict_intern(const StrDict& d, const char* g, cons
         u64 k = *reinterpret_cast<volatile u64*>(d.keys + slot);
         if (k == 0) {
             const u64 old = atomicCAS(d.keys + slot, 0ull, key);
-            if (old == 0) { atomicMin(d.first_off + slot, (u32)s); return slot; }
+            if (old == 0) { atomicMin(d.first_off + slot, s); return slot; }
             k = old;
         }
         if (k == key) {
             u32 f;
             while ((f = *reinterpret_cast<volatile u32*>(d.first_off + slot)) == kNoOffset) __nanosleep(20);   // claimer is publishing
-            bool same = true;
-            for (u32 i = 0; i < len && same; i++) same = g[f + i] == t[s + i];
-            if (same) { if ((u32)s < f) atomicMin(d.first_off + slot, (u32)s); return slot; }     // hot slots: almost never an atomic
+            bool same = true, slow = esc;
+            for (u32 i = 0; !slow && i < len && same; i++) { const char c = t[f + i]; slow = c == '\\'; same = c == t[s + i]; }
+            if (slow) {
+                ptejson::Unescape<T> x(t, f), y(t, s);
+                same = true;
+                for (u32 i = 0; i < len && same; i++) same = x.next() == y.next();
+            }
+            if (same) { if (s < f) atomicMin(d.first_off + slot, s); return slot; }     // hot slots: almost never an atomic
         }
         slot = (slot + 1) & d.mask;
     }
-    atomicMax(err, (u32)kJsonDictFull);
+    bad = kJsonDictFull;
     return 0;
 }
 
 // ---- kernels ------------------------------------------------------------------------------------------
 static constexpr int kJsonChunk = 4096;     // bytes of text per block in the newline kernels
 
+// newline mask of the 16 bytes at t + base (bit k = byte k); bytes at or behind len are not looked at.
+// The text buffer is 256-byte aligned and zero-padded behind len (pte_ingest_json).
+__device__ __forceinline__ u32 newline_mask16(const char* __restrict__ t, u64 len, u64 base) {
+    if (base >= len) return 0;
+    const uint4 v = __ldcs(reinterpret_cast<const uint4*>(t + base));
+    return ptejson::eq4(v.x, 0x0A0A0A0Au) | (ptejson::eq4(v.y, 0x0A0A0A0Au) << 4) | (ptejson::eq4(v.z, 0x0A0A0A0Au) << 8) |
+           (ptejson::eq4(v.w, 0x0A0A0A0Au) << 12);
+}
+
 __global__ void __launch_bounds__(256) json_count_newlines_kernel(const char* __restrict__ t, u64 len, u32* __restrict__ chunk_count) {
     __shared__ u32 s_w[8];
     const u64 n_chunks = (len + kJsonChunk - 1) / kJsonChunk;
     for (u64 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
-        u32 cnt = 0;
-        for (u32 k = threadIdx.x; k < kJsonChunk; k += 256) {
-            const u64 i = c * kJsonChunk + k;
-            cnt += i < len && t[i] == '\n';
-        }
+        u32 cnt = __popc(newline_mask16(t, len, c * kJsonChunk + threadIdx.x * 16));
         cnt = __reduce_add_sync(0xffffffffu, cnt);
         if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = cnt;
         __syncthreads();
@@ -101,9 +131,8 @@ json_list_newlines_kernel(const char* __restrict__ t, u64 len, const u64* __rest
     const u64 n_chunks = (len + kJsonChunk - 1) / kJsonChunk;
     for (u64 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
         // each warp owns 512 consecutive bytes of the chunk, each lane 16 consecutive bytes of those
-        const u64 base = c * kJsonChunk + warp * 512 + lane * 16;
-        u32 bits = 0;
-        for (u32 k = 0; k < 16; k++) bits |= (u32)(base + k < len && t[base + k] == '\n') << k;
+        const u64 base = c * kJsonChunk + threadIdx.x * 16;
+        u32 bits = newline_mask16(t, len, base);
         const u32 mine = __popc(bits);
         u32 inc = mine;
 #pragma unroll
@@ -126,76 +155,130 @@ struct JsonArgs {
     u32* err;          // [0] worst error code, [1] (via atomicMin) first bad line + 1
 };
 
-__device__ __forceinline__ int hex_val(char c) {
-    if (c >= '0' && c <= '9') return c - '0';
-    if (c >= 'a' && c <= 'f') return c - 'a' + 10;
-    if (c >= 'A' && c <= 'F') return c - 'A' + 10;
-    return -1;
+// ---- the five fields -> codes -------------------------------------------------------------------------
+// (templates over where the bytes come from: the text, or a few decoded bytes in local memory)
+template <typename A>
+__device__ __forceinline__ bool parse_type(const A& t, u32 s, u32 len, u32& type) {
+    // event['type'] (pod_watcher.py:267): ADDED / MODIFIED / DELETED, anything else is rejected
+    const char c0 = len ? t[s] : '\0';
+    const char* name;
+    if (len == 5 && c0 == 'A') { type = kTypeAdded; name = "ADDED"; }
+    else if (len == 8 && c0 == 'M') { type = kTypeModified; name = "MODIFIED"; }
+    else if (len == 7 && c0 == 'D') { type = kTypeDeleted; name = "DELETED"; }
+    else return false;
+    bool ok = true;
+    for (u32 k = 1; k < len; k++) ok = ok && t[s + k] == name[k];
+    return ok;
+}
+template <typename A>
+__device__ __forceinline__ bool parse_uid(const A& t, u32 s, u32 len, u64& hi, u64& lo) {
+    // metadata.uid (:164): 32 hex digits, dashes ignored
+    u32 nd = 0;
+    hi = lo = 0;
+    for (u32 k = 0; k < len; k++) {
+        const char c = t[s + k];
+        if (c == '-') continue;
+        const int v = ptejson::hex_digit(c);
+        if (v < 0 || nd >= 32) return false;
+        if (nd < 16) hi = (hi << 4) | (u64)v; else lo = (lo << 4) | (u64)v;
+        nd++;
+    }
+    return nd == 32 && (hi | lo) != 0;
+}
+template <typename A>
+__device__ __forceinline__ bool parse_rv(const A& t, u32 s, u32 len, u64& rv) {
+    if (len == 0 || len > 20) return false;
+    rv = 0;
+    for (u32 k = 0; k < len; k++) {
+        const char c = t[s + k];
+        if (c < '0' || c > '9') return false;
+        rv = rv * 10 + (u64)(c - '0');
+    }
+    return true;
+}
+template <typename A>
+__device__ __forceinline__ u32 known_phase(const A& t, u32 s, u32 len) {
+    const char* known[5] = {"Pending", "Running", "Succeeded", "Failed", "Unknown"};
+    const u32 klen[5] = {7, 7, 9, 6, 7};
+    for (u32 c = 0; c < 5; c++) {
+        if (len != klen[c]) continue;
+        bool same = true;
+        for (u32 k = 0; k < klen[c] && same; k++) same = t[s + k] == known[c][k];
+        if (same) return c;
+    }
+    return 0xFFu;
+}
+// decoded bytes of a short string spelled with escapes.  0: n bytes in buf, 1: longer than cap, 2: broken escape
+static constexpr u32 kJsonSmall = 40;
+template <typename T>
+__device__ __noinline__ u32 decode_small(const T& t, u32 s, u32 raw_len, char* buf, u32& n) {
+    ptejson::Unescape<T> u(t, s);
+    n = 0;
+    while (u.pos < s + raw_len || u.n_queue) {
+        const u32 b = u.next();
+        if (u.bad) return 2;
+        if (n == kJsonSmall) return 1;
+        buf[n++] = (char)b;
+    }
+    return u.pos > s + raw_len ? 2u : 0u;
 }
 
-// One line [p, end) of the text -> row i of the columns.  t gives access to the line's bytes by their offset in the text.
+// One line [p, end) of the text -> row i of the columns.
 template <typename T>
-__device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, u64 p, u64 end) {
-    {
-        u32 bad = kJsonOk;
-        JsonFields f;
-        u64 hi = 0, lo = 0, rv = i + 1;
-        u32 type = 0, phase = kPhNoStatus, ns = 0;
-        if (!ptejson::scan_line(t, p, end, f)) bad = kJsonMalformed;
-        if (!bad && (span_has_backslash(t, f.type) || span_has_backslash(t, f.uid) || span_has_backslash(t, f.ns) ||
-                     span_has_backslash(t, f.rv) || span_has_backslash(t, f.phase))) bad = kJsonEscapedField;
-        if (!bad) {
-            // event['type'] (pod_watcher.py:267): ADDED / MODIFIED / DELETED, anything else is rejected
-            const char c0 = f.type.present && f.type.len ? t[f.type.s] : 0;
-            if (f.type.present && f.type.len == 5 && c0 == 'A') type = kTypeAdded;
-            else if (f.type.present && f.type.len == 8 && c0 == 'M') type = kTypeModified;
-            else if (f.type.present && f.type.len == 7 && c0 == 'D') type = kTypeDeleted;
-            else bad = kJsonBadType;
-            const char* names[3] = {"ADDED", "MODIFIED", "DELETED"};
-            if (!bad) for (u32 k = 0; k < f.type.len; k++) if (t[f.type.s + k] != names[type][k]) bad = kJsonBadType;
-        }
-        if (!bad) {
-            // metadata.uid (:164): 32 hex digits, dashes ignored
-            u32 nd = 0;
-            for (u32 k = 0; f.uid.present && k < f.uid.len; k++) {
-                const char c = t[f.uid.s + k];
-                if (c == '-') continue;
-                const int v = hex_val(c);
-                if (v < 0 || nd >= 32) { nd = 99; break; }
-                if (nd < 16) hi = (hi << 4) | (u64)v; else lo = (lo << 4) | (u64)v;
-                nd++;
-            }
-            if (nd != 32 || (hi | lo) == 0) bad = kJsonBadUid;
-        }
-        if (!bad && f.rv.present) {
-            rv = 0;
-            if (f.rv.len == 0 || f.rv.len > 20) bad = kJsonBadRv;
-            for (u32 k = 0; !bad && k < f.rv.len; k++) {
-                const char c = t[f.rv.s + k];
-                if (c < '0' || c > '9') bad = kJsonBadRv; else rv = rv * 10 + (u64)(c - '0');
-            }
-        }
-        if (!bad) {
-            ns = dict_intern(a.ns_dict, a.text, t, f.ns.present ? f.ns.s : p, f.ns.present ? f.ns.len : 0, a.err);
-            if (!f.has_status) phase = kPhNoStatus;
-            else if (!f.phase.present) phase = kPhNull;
-            else {
-                const char* known[5] = {"Pending", "Running", "Succeeded", "Failed", "Unknown"};
-                const u32 klen[5] = {7, 7, 9, 6, 7};
-                phase = 0xFFu;
-                for (u32 c = 0; c < 5 && phase == 0xFFu; c++) {
-                    if (f.phase.len != klen[c]) continue;
-                    bool same = true;
-                    for (u32 k = 0; k < klen[c] && same; k++) same = t[f.phase.s + k] == known[c][k];
-                    if (same) phase = c;
-                }
-                if (phase == 0xFFu) phase = 0x80u | dict_intern(a.phase_dict, a.text, t, f.phase.s, f.phase.len, a.err);   // remapped later
-            }
-        }
-        if (bad) { atomicMax(a.err, bad); atomicMin(a.err + 1, (u32)min(i, (u64)0xFFFFFFFEu));
-        }
-        a.uid_hi[i] = hi; a.uid_lo[i] = lo; a.rv[i] = rv; a.ns[i] = ns; a.phase[i] = (u8)phase; a.type[i] = (u8)type;
+__device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, u32 p, u32 end) {
+    using namespace ptejson;
+    u32 bad = kJsonOk;
+    JsonFields f;
+    u64 hi = 0, lo = 0, rv = i + 1;
+    u32 type = 0, phase = kPhNoStatus, ns = 0;
+    char buf[kJsonSmall];
+    u32 n = 0;
+    if (!scan_line(t, p, end, f)) bad = kJsonMalformed;
+    if (!bad) {
+        const u32 s = span_start(f.type), len = span_len(f.type);
+        bool ok = span_present(f.type);
+        if (ok && has_backslash(t, s, len)) {
+            const u32 r = decode_small(t, s, len, buf, n);
+            if (r == 2) bad = kJsonEscapedField;
+            ok = r == 0 && parse_type(LocalText{buf}, 0, n, type);
+        } else ok = ok && parse_type(t, s, len, type);
+        if (!bad && !ok) bad = kJsonBadType;
     }
+    if (!bad) {
+        const u32 s = span_start(f.uid), len = span_len(f.uid);
+        bool ok = span_present(f.uid);
+        if (ok && has_backslash(t, s, len)) {
+            const u32 r = decode_small(t, s, len, buf, n);
+            if (r == 2) bad = kJsonEscapedField;
+            ok = r == 0 && parse_uid(LocalText{buf}, 0, n, hi, lo);
+        } else ok = ok && parse_uid(t, s, len, hi, lo);
+        if (!bad && !ok) bad = kJsonBadUid;
+    }
+    if (!bad && span_present(f.rv)) {
+        const u32 s = span_start(f.rv), len = span_len(f.rv);
+        bool ok;
+        if (has_backslash(t, s, len)) {
+            const u32 r = decode_small(t, s, len, buf, n);
+            if (r == 2) bad = kJsonEscapedField;
+            ok = r == 0 && parse_rv(LocalText{buf}, 0, n, rv);
+        } else ok = parse_rv(t, s, len, rv);
+        if (!bad && !ok) bad = kJsonBadRv;
+    }
+    if (!bad) {
+        // metadata.namespace (:163): any string; a pod without one is in the namespace "" like every other such pod
+        ns = dict_intern(a.ns_dict, t, span_present(f.ns) ? span_start(f.ns) : p, span_present(f.ns) ? span_len(f.ns) : 0u, bad);
+        // status.phase (:167): NoStatus when pod.status is falsy, Null when there is no phase string
+        if (!f.has_status) phase = kPhNoStatus;
+        else if (!span_present(f.phase)) phase = kPhNull;
+        else {
+            const u32 s = span_start(f.phase), len = span_len(f.phase);
+            if (has_backslash(t, s, len)) phase = decode_small(t, s, len, buf, n) == 0 ? known_phase(LocalText{buf}, 0, n) : 0xFFu;
+            else phase = known_phase(t, s, len);
+            if (phase == 0xFFu) phase = 0x80u | dict_intern(a.phase_dict, t, s, len, bad);   // remapped later
+        }
+    }
+    if (bad) { atomicMax(a.err, bad); atomicMin(a.err + 1, (u32)min(i, (u64)0xFFFFFFFEu)); }
+    a.uid_hi[i] = hi; a.uid_lo[i] = lo; a.rv[i] = rv; a.ns[i] = ns; a.phase[i] = (u8)phase; a.type[i] = (u8)type;
 }
 
 // One thread per line, 32 consecutive lines per warp (handed out by ticket, so long and short lines even out); the
@@ -212,8 +295,8 @@ __global__ void __launch_bounds__(kJsonThreads) json_parse_kernel(JsonArgs a, u3
         if (g0 >= a.n_lines) break;
         const u64 li = g0 + lane;
         if (li < a.n_lines) {
-            const u64 p = li ? a.nl[li - 1] + 1 : 0;
-            const u64 end = li < a.n_nl ? a.nl[li] : a.len;
+            const u32 p = li ? (u32)a.nl[li - 1] + 1u : 0u;
+            const u32 end = li < a.n_nl ? (u32)a.nl[li] : (u32)a.len;
             json_line(a, t, li, p, end);
         }
         __syncwarp();

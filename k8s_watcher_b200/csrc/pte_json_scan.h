@@ -29,7 +29,13 @@ namespace ptejson {
 typedef unsigned long long u64;
 typedef unsigned int u32;
 
-struct Span { u64 s; u32 len; bool present; };
+// A string value: where its body starts in the text and how many RAW bytes it has, packed (start << 32 | len << 1 | 1)
+// so that choosing which of the five fields to set costs five predicated moves; 0 = absent.  Texts are < 4 GiB.
+typedef u64 Span;
+PTE_JS_HD Span make_span(u32 s, u32 len) { return ((u64)s << 32) | ((u64)len << 1) | 1ull; }
+PTE_JS_HD bool span_present(Span sp) { return (sp & 1ull) != 0; }
+PTE_JS_HD u32 span_start(Span sp) { return (u32)(sp >> 32); }
+PTE_JS_HD u32 span_len(Span sp) { return (u32)sp >> 1; }
 struct Fields { Span type, uid, ns, rv, phase; bool has_status; };
 
 PTE_JS_HD u32 ctz32(u32 x) {
@@ -74,34 +80,38 @@ PTE_JS_UNROLL
 enum : u32 { C_OTHER = 0, C_ROOT = 1, C_OBJECT = 2, C_META = 3, C_STATUS = 4 };
 enum : u32 { W_NONE = 0, W_TYPE = 1, W_UID = 2, W_NS = 3, W_RV = 4, W_PHASE = 5, W_OBJECT = 6, W_META = 7, W_STATUS = 8 };
 
-template <typename T>
-PTE_JS_HD bool bytes_are(const T& t, u64 s, const char* name, u32 n) {
-    for (u32 i = 0; i < n; i++) if (t[s + i] != name[i]) return false;
-    return true;
+// up to eight characters as the little-endian word a load8() of them gives
+PTE_JS_HD constexpr u64 word_of(const char* s, int n) {
+    u64 v = 0;
+    for (int i = n - 1; i >= 0; i--) v = (v << 8) | (u64)(unsigned char)s[i];
+    return v;
 }
+PTE_JS_HD constexpr u64 low_bytes(int n) { return n >= 8 ? ~0ull : ((1ull << (8 * n)) - 1ull); }
 
-// the key [s, s+len) seen in a container of meaning ctx: which value follows?  A key spelled with escapes never
-// matches (its bytes differ from the plain name), as in the reference's client, which compares decoded names --
-// nobody escapes these names, and one who did would simply not be seen.
+// the key [s, s+len) seen in a container of meaning ctx: which value follows?  Compared as one or two 8-byte words.
+// A key spelled with escapes never matches (its bytes differ from the plain name): nobody escapes these names, and
+// one who did would simply not be seen.
 template <typename T>
-PTE_JS_HD u32 key_meaning(const T& t, u64 s, u32 len, u32 ctx) {
+PTE_JS_HD u32 key_meaning(const T& t, u32 s, u32 len, u32 ctx) {
+    if (len < 3 || len > 15) return W_NONE;
+    const u64 k = t.load8(s);
     if (ctx == C_ROOT) {
-        if (len == 4 && bytes_are(t, s, "type", 4)) return W_TYPE;
-        if (len == 6 && bytes_are(t, s, "object", 6)) return W_OBJECT;
+        if (len == 4 && (k & low_bytes(4)) == word_of("type", 4)) return W_TYPE;
+        if (len == 6 && (k & low_bytes(6)) == word_of("object", 6)) return W_OBJECT;
     } else if (ctx == C_OBJECT) {
-        if (len == 8 && bytes_are(t, s, "metadata", 8)) return W_META;
-        if (len == 6 && bytes_are(t, s, "status", 6)) return W_STATUS;
+        if (len == 8 && k == word_of("metadata", 8)) return W_META;
+        if (len == 6 && (k & low_bytes(6)) == word_of("status", 6)) return W_STATUS;
     } else if (ctx == C_META) {
-        if (len == 3 && bytes_are(t, s, "uid", 3)) return W_UID;
-        if (len == 9 && bytes_are(t, s, "namespace", 9)) return W_NS;
-        if (len == 15 && bytes_are(t, s, "resourceVersion", 15)) return W_RV;
+        if (len == 3 && (k & low_bytes(3)) == word_of("uid", 3)) return W_UID;
+        if (len == 9 && k == word_of("namespac", 8) && t[s + 8] == 'e') return W_NS;
+        if (len == 15 && k == word_of("resource", 8) && (t.load8(s + 8) & low_bytes(7)) == word_of("Version", 7)) return W_RV;
     } else if (ctx == C_STATUS) {
-        if (len == 5 && bytes_are(t, s, "phase", 5)) return W_PHASE;
+        if (len == 5 && (k & low_bytes(5)) == word_of("phase", 5)) return W_PHASE;
     }
     return W_NONE;
 }
 
-PTE_JS_HD void set_field(Fields& f, u32 w, const Span& sp) {
+PTE_JS_HD void set_field(Fields& f, u32 w, Span sp) {
     if (w == W_TYPE) f.type = sp; else if (w == W_UID) f.uid = sp; else if (w == W_NS) f.ns = sp;
     else if (w == W_RV) f.rv = sp; else if (w == W_PHASE) f.phase = sp;
 }
@@ -115,33 +125,32 @@ PTE_JS_HD void set_field(Fields& f, u32 w, const Span& sp) {
 // namespace,resourceVersion}, root.object.status.phase, each container reached through exactly that key; a value that
 // is not a string leaves the field absent; of duplicate keys the last one wins (as in json.loads).
 template <typename T>
-PTE_JS_HD bool scan_line(const T& t, u64 p, u64 end, Fields& f) {
-    const Span none = {0, 0, false};
-    f.type = f.uid = f.ns = f.rv = f.phase = none;
+PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
+    f.type = f.uid = f.ns = f.rv = f.phase = 0;
     f.has_status = false;
     while (p < end && is_ws(t[p])) p++;
     if (p >= end) return false;
     { const char c = t[p]; if (c != '{' && c != '[') return false; }
 
-    const u64 kNever = ~0ull;
+    const u32 kNever = ~0u;
     u32 depth = 0, ctxs = 0, want = W_NONE, pend = W_NONE;
-    u64 want_pos = 0, pend_q = 0, last_open_q = kNever, last_close_q = kNever;
+    u32 want_pos = 0, pend_q = 0, last_open_q = kNever, last_close_q = kNever;
     bool in_str = false, esc_carry = false, bad = false;
 
     u32 w[8];
-    u64 blk = p & ~31ull;
+    u32 blk = p & ~31u;
     t.load32(blk, w);
     for (; blk < end; blk += 32) {
         u32 nx[8];
-        const bool more = blk + 32 < end;
+        const bool more = end - blk > 32;
         if (more) t.load32(blk + 32, nx);            // in flight while this block is looked at
-        const u32 lo = blk < p ? (u32)(p - blk) : 0u;
-        const u64 left = end - blk;
-        u32 valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (u32)left) - 1u);
+        const u32 lo = blk < p ? p - blk : 0u;
+        const u32 left = end - blk;
+        u32 valid = left >= 32 ? 0xFFFFFFFFu : ((1u << left) - 1u);
         valid &= ~((1u << lo) - 1u);
 
         u32 w20[8];
-PTE_JS_UNROLL
+        PTE_JS_UNROLL
         for (int k = 0; k < 8; k++) w20[k] = w[k] | 0x20202020u;
         u32 Q = eq32(w, 0x22222222u) & valid;                 // "
         const u32 B = eq32(w, 0x5C5C5C5Cu) & valid;           // backslash
@@ -151,7 +160,7 @@ PTE_JS_UNROLL
 
         // which bytes are escaped: every backslash that is not itself escaped escapes its successor
         if (B | (u32)esc_carry) {
-            u32 escaped = esc_carry ? (1u << lo) : 0u;         // (lo: the first valid byte; a carry only exists past the first block)
+            u32 escaped = esc_carry ? 1u : 0u;                 // a carry only arrives in a block that starts at its bit 0
             u32 m = B & ~escaped;
             esc_carry = false;
             while (m) {
@@ -169,13 +178,12 @@ PTE_JS_UNROLL
         const u32 openq = Q & s, closeq = Q & ~s;
 
         // a field's value string opened earlier (at pend_q) and not closed yet: the next quote behind pend_q closes it
-        if (pend != W_NONE && Q && pend_q < blk + 32) {
+        if (pend != W_NONE && Q) {
             u32 m = Q;
-            if (pend_q >= blk) m &= ~((2u << (u32)(pend_q - blk)) - 1u);
+            if (pend_q >= blk) m = pend_q - blk >= 32 ? 0u : (m & ~((2u << (pend_q - blk)) - 1u));
             if (m) {
-                const u64 e = blk + ctz32(m);
-                const Span sp = {pend_q + 1, (u32)(e - pend_q - 1), true};
-                set_field(f, pend, sp);
+                const u32 e = blk + ctz32(m);
+                set_field(f, pend, make_span(pend_q + 1, e - pend_q - 1));
                 pend = W_NONE;
             }
         }
@@ -191,7 +199,7 @@ PTE_JS_UNROLL
                 const u32 i = ctz32(ev);
                 const u32 bit = 1u << i;
                 ev &= ev - 1;
-                const u64 pos = blk + i;
+                const u32 pos = blk + i;
                 if (Os & bit) {
                     if (depth < 3) {
                         u32 nc = C_OTHER;
@@ -199,7 +207,7 @@ PTE_JS_UNROLL
                             if (depth == 0) nc = C_ROOT;
                             else if (want != W_NONE) {
                                 bool adjacent = true;               // the container must BE the value of that key
-                                for (u64 q = want_pos + 1; q < pos; q++) adjacent = adjacent && is_ws(t[q]);
+                                for (u32 q = want_pos + 1; q < pos; q++) adjacent = adjacent && is_ws(t[q]);
                                 if (adjacent) {
                                     if (want == W_OBJECT) nc = C_OBJECT;
                                     else if (want == W_META) nc = C_META;
@@ -214,30 +222,30 @@ PTE_JS_UNROLL
                 } else if (Cs & bit) {
                     if (depth == 0) bad = true; else depth--;
                     want = W_NONE;
-                } else if (depth >= 1 && depth <= 3) {
+                } else {
                     want = W_NONE;
-                    const u32 ctx = (ctxs >> (4 * depth)) & 15u;
+                    const u32 ctx = depth <= 3 ? (ctxs >> (4 * depth)) & 15u : (u32)C_OTHER;     // (nibble 0 is never set)
                     if (ctx != C_OTHER) {
                         // the key: the last complete string in front of this colon
                         const u32 below = bit - 1u;
-                        const u64 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
-                        const u64 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
+                        const u32 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
+                        const u32 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
                         if (ks != kNever && ke != kNever && ke > ks) {
-                            const u32 wv = key_meaning(t, ks + 1, (u32)(ke - ks - 1), ctx);
+                            const u32 wv = key_meaning(t, ks + 1, ke - ks - 1, ctx);
                             if (wv >= W_OBJECT) { want = wv; want_pos = pos; }
                             else if (wv != W_NONE) {
-                                set_field(f, wv, none);              // a later duplicate wins, string or not
+                                set_field(f, wv, 0);                 // a later duplicate wins, string or not
                                 pend = W_NONE;
-                                u64 q = pos + 1;
-                                while (q < end && is_ws(t[q])) q++;
-                                if (q < end && t[q] == '"') {
+                                u32 q = pos + 1;
+                                char c = q < end ? t[q] : '\0';
+                                while (is_ws(c)) { q++; c = q < end ? t[q] : '\0'; }
+                                if (c == '"') {
                                     pend = wv; pend_q = q;
-                                    if (q < blk + 32) {
-                                        const u32 m = Q & ~((2u << (u32)(q - blk)) - 1u);
+                                    if (q - blk < 32) {
+                                        const u32 m = Q & ~((2u << (q - blk)) - 1u);
                                         if (m) {
-                                            const u64 e = blk + ctz32(m);
-                                            const Span sp = {q + 1, (u32)(e - q - 1), true};
-                                            set_field(f, wv, sp);
+                                            const u32 e = blk + ctz32(m);
+                                            set_field(f, wv, make_span(q + 1, e - q - 1));
                                             pend = W_NONE;
                                         }
                                     }
@@ -245,19 +253,86 @@ PTE_JS_UNROLL
                             }
                         }
                     }
-                } else {
-                    want = W_NONE;
                 }
             }
         }
         if (openq) last_open_q = blk + top32(openq);
         if (closeq) last_close_q = blk + top32(closeq);
         if (more) {
-PTE_JS_UNROLL
+            PTE_JS_UNROLL
             for (int k = 0; k < 8; k++) w[k] = nx[k];
         }
     }
     return depth == 0 && !in_str && !bad && pend == W_NONE;
+}
+
+// ---- escape sequences -------------------------------------------------------------------------------------
+// The bytes a JSON string body stands for, one at a time: \" \\ \/ \b \f \n \r \t and \uXXXX (UTF-8 encoded, surrogate pairs
+// joined).  `bad` is set by anything else behind a backslash and by a surrogate without its partner.
+PTE_JS_HD int hex_digit(char c) {
+    if (c >= '0' && c <= '9') return c - '0';
+    if (c >= 'a' && c <= 'f') return c - 'a' + 10;
+    if (c >= 'A' && c <= 'F') return c - 'A' + 10;
+    return -1;
+}
+template <typename T>
+struct Unescape {
+    const T& t;
+    u32 pos;          // next raw byte
+    u32 queue;        // decoded bytes not handed out yet (low byte first)
+    u32 n_queue;
+    bool bad;
+    PTE_JS_HD Unescape(const T& t_, u32 s) : t(t_), pos(s), queue(0), n_queue(0), bad(false) {}
+    PTE_JS_HD int hex4(u32 at) const {
+        int v = 0;
+        for (u32 k = 0; k < 4; k++) { const int d = hex_digit(t[at + k]); if (d < 0) return -1; v = v * 16 + d; }
+        return v;
+    }
+    // the next decoded byte; the caller stops by count or by watching pos reach the closing quote (with n_queue == 0)
+    PTE_JS_HD u32 next() {
+        if (n_queue) { const u32 b = queue & 0xFFu; queue >>= 8; n_queue--; return b; }
+        const char c = t[pos++];
+        if (c != '\\') return (u32)(unsigned char)c;
+        const char e = t[pos++];
+        switch (e) {
+            case '"': return '"';
+            case '\\': return '\\';
+            case '/': return '/';
+            case 'b': return 8;
+            case 'f': return 12;
+            case 'n': return 10;
+            case 'r': return 13;
+            case 't': return 9;
+            case 'u': break;
+            default: bad = true; return (u32)(unsigned char)e;
+        }
+        int cp = hex4(pos);
+        if (cp < 0) { bad = true; return 0; }
+        pos += 4;
+        if (cp >= 0xDC00 && cp <= 0xDFFF) { bad = true; return 0; }
+        if (cp >= 0xD800 && cp <= 0xDBFF) {
+            const int lo = (t[pos] == '\\' && t[pos + 1] == 'u') ? hex4(pos + 2) : -1;
+            if (lo < 0xDC00 || lo > 0xDFFF) { bad = true; return 0; }
+            pos += 6;
+            cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+        }
+        if (cp < 0x80) return (u32)cp;
+        if (cp < 0x800) { queue = 0x80u | (cp & 0x3F); n_queue = 1; return 0xC0u | (cp >> 6); }
+        if (cp < 0x10000) { queue = (0x80u | ((cp >> 6) & 0x3F)) | ((0x80u | (cp & 0x3F)) << 8); n_queue = 2; return 0xE0u | (cp >> 12); }
+        queue = (0x80u | ((cp >> 12) & 0x3F)) | ((0x80u | ((cp >> 6) & 0x3F)) << 8) | ((0x80u | (cp & 0x3F)) << 16);
+        n_queue = 3;
+        return 0xF0u | (cp >> 18);
+    }
+};
+
+// decoded length of the string body [s, s + raw_len); sets bad like Unescape
+template <typename T>
+PTE_JS_HD u32 decoded_length(const T& t, u32 s, u32 raw_len, bool& bad) {
+    Unescape<T> u(t, s);
+    u32 n = 0;
+    while (u.pos < s + raw_len || u.n_queue) { u.next(); n++; if (u.bad) break; }
+    bad = u.bad || u.pos > s + raw_len;       // an escape cut off by the closing quote cannot happen (the quote would be escaped), but a count is cheap
+    return n;
 }
 
 }  // namespace ptejson

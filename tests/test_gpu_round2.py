@@ -364,3 +364,61 @@ def test_pipelined_replay_without_rv_column_for_arrival_ordered_logs():
         words, st = e.replay_pipelined(junk, chunk_events=32_768, with_namespaces=False, with_rv=False)
         bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n]
         assert np.array_equal(np.flatnonzero(bits).astype(np.uint64), want) and st["n_emitted"] == ost["n_emitted"]
+
+
+# ---- watch JSON spelled with escape sequences: strings are what they stand for ------------------
+def _respell(text: str, rnd) -> str:
+    """The JSON string body of `text` with some characters written as \\uXXXX (or the short escapes)."""
+    out = []
+    for ch in text:
+        r = rnd.random()
+        cp = ord(ch)
+        if cp > 0xFFFF:
+            hi, lo = 0xD800 + ((cp - 0x10000) >> 10), 0xDC00 + ((cp - 0x10000) & 0x3FF)
+            out.append("\\u%04x\\u%04X" % (hi, lo) if r < 0.5 else ch)
+        elif ch in '"\\' or cp < 0x20:
+            out.append(json.dumps(ch)[1:-1])
+        elif r < 0.25:
+            out.append("\\u%04x" % cp if rnd.random() < 0.5 else "\\u%04X" % cp)
+        elif ch == "/" and r < 0.6:
+            out.append("\\/")
+        else:
+            out.append(ch)
+    return "".join(out)
+
+
+@pytest.mark.gpu
+def test_device_json_decodes_escapes_in_every_field_it_reads():
+    import random
+    rnd = random.Random(99)
+    n, pods = 6000, 150
+    cols = c_oracle.generate(SEED, n, pods, dist=1, p_del=0.1, p_nostatus=0.05, p_null=0.05)
+    events = fk.events_from_columns(cols)
+    odd_ns = ['quo"te', "back\\slash", "sl/ash", "é中\U0001f600", "tab\there", "plain-but-new"]
+    odd_ph = ["Terminating", 'Weird"Phase', "Évicted\U0001f4a5"]
+    for k, ev in enumerate(events):
+        if k % 5 == 0:
+            ev["object"].metadata.namespace = odd_ns[(k // 5) % len(odd_ns)]
+        if k % 7 == 0 and ev["object"].status is not None:
+            ev["object"].status.phase = odd_ph[(k // 7) % len(odd_ph)]
+    lines = fk.watch_json_lines(events, seed=4).split(b"\n")
+    lines = [l for l in lines if l]
+    assert len(lines) == n
+    out = []
+    for ev, line in zip(events, lines):
+        text = line.decode()
+        md, st = ev["object"].metadata, ev["object"].status
+        vals = [ev["type"], md.uid, md.namespace, md.resource_version] + ([st.phase] if st is not None and st.phase is not None else [])
+        for v in vals:
+            for spelled in {json.dumps(v), json.dumps(v, ensure_ascii=False)}:
+                text = text.replace(spelled, '"' + _respell(v, rnd) + '"')
+        assert json.loads(text) == json.loads(line)          # same document, other spelling
+        out.append(text.encode())
+    text = b"\n".join(out) + b"\n"
+    want = ReplayLog.from_events(events)
+    with PhaseTransitionEngine(n, pods) as e:
+        got = ReplayLog.from_watch_json(e, text)
+    for k in ("uid_hi", "uid_lo", "rv", "type"):
+        assert np.array_equal(got.columns[k], want.columns[k]), k
+    assert got.namespaces == want.namespaces and np.array_equal(got.columns["ns_id"], want.columns["ns_id"])
+    assert got.phases == want.phases and np.array_equal(got.columns["phase"], want.columns["phase"])

@@ -152,3 +152,28 @@ def test_random_documents(scan):
         sep = rnd.choice([(",", ":"), (", ", ": "), (" ,  ", "  :   ")])
         line = json.dumps(doc, separators=sep, ensure_ascii=rnd.random() < 0.5).encode()
         check(scan, line, shifts=(i % 32, (i * 7) % 64))
+
+
+def test_unescape_matches_json_loads(scan, tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("jsonscan2") / "libjsonscan.so")
+    subprocess.run(["g++", "-O1", "-shared", "-fPIC", "-o", so, os.path.join(ROOT, "tests", "json_scan_harness.cpp")], check=True)
+    lib = ctypes.CDLL(so)
+    lib.unescape_host.argtypes = [ctypes.c_char_p, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_char_p, ctypes.c_ulonglong]
+    lib.unescape_host.restype = ctypes.c_longlong
+
+    def dec(body: bytes):
+        buf = b"xx" + body + b'"' + b"\xff" * 16
+        out = ctypes.create_string_buffer(4 * len(body) + 8)
+        n = lib.unescape_host(buf, 2, len(body), out, len(out))
+        return None if n < 0 else out.raw[:n]
+    rnd = random.Random(5)
+    alphabet = ['a', 'Z', '"', '\\', '/', '\b', '\f', '\n', '\r', '\t', 'é', '中', '\U0001f600', '\x00', '\x7f', ' ', '߿', 'ࠀ', '￿']
+    for i in range(3000):
+        text = "".join(rnd.choice(alphabet) for _ in range(rnd.randrange(0, 12)))
+        body = json.dumps(text, ensure_ascii=rnd.random() < 0.7).encode()[1:-1]
+        if rnd.random() < 0.3:
+            body = body.replace(b"/", b"\\/")
+        assert dec(body) == text.encode(), body
+    assert dec(b"\\u0041\\u00e9\\ud83d\\ude00") == "Aé\U0001f600".encode()
+    for broken in (b"\\q", b"\\u12", b"\\u12zz", b"\\ud83d", b"\\ud83dx", b"\\ud83d\\u0041", b"\\ude00"):
+        assert dec(broken) is None, broken
