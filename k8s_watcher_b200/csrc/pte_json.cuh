@@ -284,8 +284,11 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
 // One thread per line, 32 consecutive lines per warp (handed out by ticket, so long and short lines even out); the
 // text comes straight from global memory in 32-byte blocks, the next block in flight while the current one is scanned.
 static constexpr int kJsonThreads = 128;
+#ifndef PTE_JSON_BLOCKS
+#define PTE_JSON_BLOCKS 6      // 8 (64 registers, spills) measured slower: 2.36 vs 2.30 ms per GB
+#endif
 
-__global__ void __launch_bounds__(kJsonThreads) json_parse_kernel(JsonArgs a, u32* __restrict__ ticket) {
+__global__ void __launch_bounds__(kJsonThreads, PTE_JSON_BLOCKS) json_parse_kernel(JsonArgs a, u32* __restrict__ ticket) {
     const u32 lane = threadIdx.x & 31;
     const GlobalText t{a.text};
     for (;;) {

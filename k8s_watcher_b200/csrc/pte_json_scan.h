@@ -133,8 +133,8 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
     { const char c = t[p]; if (c != '{' && c != '[') return false; }
 
     const u32 kNever = ~0u;
-    u32 depth = 0, ctxs = 0, want = W_NONE, pend = W_NONE;
-    u32 want_pos = 0, pend_q = 0, last_open_q = kNever, last_close_q = kNever;
+    u32 depth = 0, ctxs = 0, pend = W_NONE;
+    u32 pend_q = 0, last_open_q = kNever, last_close_q = kNever;
     bool in_str = false, esc_carry = false, bad = false;
 
     u32 w[8];
@@ -188,68 +188,88 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
             }
         }
 
-        const u32 Os = O & ~s, Cs = C & ~s;
+        // Brackets outside strings are walked one by one (they carry the nesting and say what a container means); colons
+        // are not: the colons between two brackets all belong to the container open there, so they are collected by mask
+        // and only those directly inside root / metadata / status are looked at, after the walk, when all lanes of the
+        // warp are back together.
+        const u32 Os = O & ~s, Cs = C & ~s, Ks = K & ~s;
         const u32 n_close = popc32(Cs);
+        u32 cand_root = 0, cand_meta = 0, cand_status = 0;
         if (depth >= 4 + n_close) {
             // too deep for anything in this block to matter: only the nesting changes
             depth += popc32(Os) - n_close;
         } else {
-            u32 ev = Os | Cs | (K & ~s);
-            while (ev) {
-                const u32 i = ctz32(ev);
+            u32 br = Os | Cs, done = 0;
+            for (;;) {
+                const u32 i = br ? ctz32(br) : 32u;
+                const u32 upto = i >= 32 ? 0xFFFFFFFFu : ((1u << i) - 1u);
+                const u32 ctx = depth <= 3 ? (ctxs >> (4 * depth)) & 15u : (u32)C_OTHER;      // (nibble 0 is never set)
+                const u32 seg = Ks & upto & ~done;
+                if (ctx == C_ROOT) cand_root |= seg; else if (ctx == C_META) cand_meta |= seg; else if (ctx == C_STATUS) cand_status |= seg;
+                if (i >= 32) break;
                 const u32 bit = 1u << i;
-                ev &= ev - 1;
-                const u32 pos = blk + i;
-                if (Os & bit) {
+                done = upto | bit;
+                br &= br - 1;
+                if (Cs & bit) {
+                    if (depth == 0) bad = true; else depth--;
+                } else {
                     if (depth < 3) {
+                        const u32 pos = blk + i;
                         u32 nc = C_OTHER;
                         if (t[pos] == '{') {
                             if (depth == 0) nc = C_ROOT;
-                            else if (want != W_NONE) {
-                                bool adjacent = true;               // the container must BE the value of that key
-                                for (u32 q = want_pos + 1; q < pos; q++) adjacent = adjacent && is_ws(t[q]);
-                                if (adjacent) {
-                                    if (want == W_OBJECT) nc = C_OBJECT;
-                                    else if (want == W_META) nc = C_META;
-                                    else if (want == W_STATUS) { nc = C_STATUS; f.has_status = true; }   // pod.status is truthy
+                            else if (ctx == C_ROOT || ctx == C_OBJECT) {
+                                // the container means something only as the value of "object" / "metadata" / "status":
+                                // key string, colon, container, with nothing but whitespace in between
+                                const u32 below = bit - 1u;
+                                const u32 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
+                                const u32 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
+                                if (ks != kNever && ke != kNever && ke > ks) {
+                                    u32 colons = 0;
+                                    bool clean = true;
+                                    for (u32 q = ke + 1; q < pos; q++) { const char c = t[q]; colons += c == ':'; clean = clean && (c == ':' || is_ws(c)); }
+                                    if (clean && colons == 1) {
+                                        const u32 wv = key_meaning(t, ks + 1, ke - ks - 1, ctx);
+                                        if (wv == W_OBJECT) nc = C_OBJECT;
+                                        else if (wv == W_META) nc = C_META;
+                                        else if (wv == W_STATUS) { nc = C_STATUS; f.has_status = true; }   // pod.status is truthy
+                                    }
                                 }
                             }
                         }
                         ctxs = (ctxs & ~(15u << (4 * (depth + 1)))) | (nc << (4 * (depth + 1)));
                     }
                     depth++;
-                    want = W_NONE;
-                } else if (Cs & bit) {
-                    if (depth == 0) bad = true; else depth--;
-                    want = W_NONE;
-                } else {
-                    want = W_NONE;
-                    const u32 ctx = depth <= 3 ? (ctxs >> (4 * depth)) & 15u : (u32)C_OTHER;     // (nibble 0 is never set)
-                    if (ctx != C_OTHER) {
-                        // the key: the last complete string in front of this colon
-                        const u32 below = bit - 1u;
-                        const u32 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
-                        const u32 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
-                        if (ks != kNever && ke != kNever && ke > ks) {
-                            const u32 wv = key_meaning(t, ks + 1, ke - ks - 1, ctx);
-                            if (wv >= W_OBJECT) { want = wv; want_pos = pos; }
-                            else if (wv != W_NONE) {
-                                set_field(f, wv, 0);                 // a later duplicate wins, string or not
+                }
+            }
+        }
+        u32 cand = cand_root | cand_meta | cand_status;
+        while (cand) {
+            const u32 i = ctz32(cand);
+            const u32 bit = 1u << i;
+            cand &= cand - 1;
+            const u32 pos = blk + i;
+            const u32 ctx = (cand_root & bit) ? (u32)C_ROOT : (cand_meta & bit) ? (u32)C_META : (u32)C_STATUS;
+            // the key: the last complete string in front of this colon
+            const u32 below = bit - 1u;
+            const u32 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
+            const u32 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
+            if (ks != kNever && ke != kNever && ke > ks) {
+                const u32 wv = key_meaning(t, ks + 1, ke - ks - 1, ctx);
+                if (wv != W_NONE && wv < W_OBJECT) {
+                    set_field(f, wv, 0);                 // a later duplicate wins, string or not
+                    pend = W_NONE;
+                    u32 q = pos + 1;
+                    char c = q < end ? t[q] : '\0';
+                    while (is_ws(c)) { q++; c = q < end ? t[q] : '\0'; }
+                    if (c == '"') {
+                        pend = wv; pend_q = q;
+                        if (q - blk < 32) {
+                            const u32 m = Q & ~((2u << (q - blk)) - 1u);
+                            if (m) {
+                                const u32 e = blk + ctz32(m);
+                                set_field(f, wv, make_span(q + 1, e - q - 1));
                                 pend = W_NONE;
-                                u32 q = pos + 1;
-                                char c = q < end ? t[q] : '\0';
-                                while (is_ws(c)) { q++; c = q < end ? t[q] : '\0'; }
-                                if (c == '"') {
-                                    pend = wv; pend_q = q;
-                                    if (q - blk < 32) {
-                                        const u32 m = Q & ~((2u << (q - blk)) - 1u);
-                                        if (m) {
-                                            const u32 e = blk + ctz32(m);
-                                            set_field(f, wv, make_span(q + 1, e - q - 1));
-                                            pend = W_NONE;
-                                        }
-                                    }
-                                }
                             }
                         }
                     }

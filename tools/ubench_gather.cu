@@ -16,13 +16,15 @@ __device__ __forceinline__ u64 mix64(u64 z) {
     return z ^ (z >> 31);
 }
 
-enum { PLAIN16, CG16, NC16, EVICT_FIRST16, EVICT_LAST16, NOALLOC16, PF64_16, PF128_16, PLAIN8, PAIR32, CV16, N_MODES };
+enum { PLAIN16, CG16, NC16, EVICT_FIRST16, EVICT_LAST16, NOALLOC16, PF64_16, PF128_16, PLAIN8, PAIR32, CV16, CAS128, CAS64, RELAXED16, N_MODES };
 const char* kNames[N_MODES] = {"ld.global.v2.u64", "ld.global.cg.v2.u64", "ld.global.nc.v2.u64", "cache_hint evict_first", "cache_hint evict_last",
-                               "L1::no_allocate", "ld.global.L2::64B", "ld.global.L2::128B", "ld.global.u64 (8 B)", "2 x 16 B in one sector", "ld.volatile (cv)"};
+                               "L1::no_allocate", "ld.global.L2::64B", "ld.global.L2::128B", "ld.global.u64 (8 B)", "2 x 16 B in one sector", "ld.volatile (cv)",
+                               "atom.cas.b128 (never matches)", "atom.cas.b64 (never matches)", "ld.relaxed.gpu.v2.u64"};
 
 template <int MODE>
 __device__ __forceinline__ u64 probe(const ulonglong2* t, u64 slot, u64 pol) {
     const ulonglong2* p = t + slot;
+    (void)p;
     ulonglong2 v = make_ulonglong2(0, 0);
     if (MODE == PLAIN16) asm volatile("ld.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     if (MODE == CG16) asm volatile("ld.global.cg.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
@@ -33,6 +35,12 @@ __device__ __forceinline__ u64 probe(const ulonglong2* t, u64 slot, u64 pol) {
     if (MODE == NOALLOC16) asm volatile("ld.global.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     if (MODE == PF64_16) asm volatile("ld.global.L2::64B.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     if (MODE == PF128_16) asm volatile("ld.global.L2::128B.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    if (MODE == CAS128) {         // served by the slice that owns the line: does the other die keep a copy of what an atomic read?
+        asm volatile("{ .reg .b128 c, n, o; mov.b128 c, {%3, %3}; mov.b128 n, {%4, %4}; atom.global.cas.b128 o, [%2], c, n; mov.b128 {%0, %1}, o; }"
+                     : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(0ull), "l"(5ull) : "memory");
+    }
+    if (MODE == CAS64) asm volatile("atom.global.cas.b64 %0, [%1], %2, %3;" : "=l"(v.x) : "l"(p), "l"(0ull), "l"(5ull) : "memory");
+    if (MODE == RELAXED16) asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
     if (MODE == PLAIN8) asm volatile("ld.global.u64 %0, [%1];" : "=l"(v.x) : "l"(p));
     if (MODE == PAIR32) {
         const ulonglong2* q = t + (slot & ~1ull);
@@ -118,6 +126,9 @@ int main(int argc, char** argv) {
     run<PF128_16>(t, slots, out);
     run<PLAIN8>(t, slots, out);
     run<PAIR32>(t, slots, out);
+    run<CAS128>(t, slots, out);
+    run<CAS64>(t, slots, out);
+    run<RELAXED16>(t, slots, out);
     cudaError_t e = cudaDeviceSynchronize();
     printf("%s\n", cudaGetErrorString(e));
     return e == cudaSuccess ? 0 : 1;
