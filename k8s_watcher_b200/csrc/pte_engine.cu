@@ -5,6 +5,7 @@
 #include "pte_kernels.cuh"
 #include "pte_partition.cuh"
 #include "pte_json.cuh"
+#include "pte_tiny.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h>
@@ -107,6 +108,12 @@ struct pte_engine {
     int scatter_cfg = 0, scatter_occ = 1, scatter_tile = 6144, scatter_threads = 512;
     u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
     u8 *state_old = nullptr, *state_new = nullptr;           // per dictionary slot: last known phase of the stream
+    // small batches in one launch (pte_tiny.cuh): packed staging in pinned host memory and on the device
+    bool tiny_on = true;                                     // PTE_TINY=0: every batch takes the bulk kernels
+    u8 *tiny_in_host = nullptr, *tiny_in_dev = nullptr;      // uid_hi | uid_lo | rv | ns | phase | type of one batch
+    u8 *tiny_out_host = nullptr, *tiny_out_dev = nullptr;    // Counters | out_idx | out_type of one batch
+    bool tiny_staged = false;                                // the batch is in tiny_in_dev, not yet in the column arrays
+    bool tiny_result = false;                                // tiny_out_host holds the notifications of the last run
     bool carry_valid = false;                                // dictionary + state hold a stream that can be continued
     LogColumns shadow{};                                     // rv-ordered copy of an unordered log (allocated on first use)
     u32* perm = nullptr;                                     // shadow row -> arrival index
@@ -531,8 +538,10 @@ void pte_destroy(pte_handle h) {
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
                     h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
                     h->pay_frag_off, h->pay_rec_off, h->pay_tile_off, h->json_text, h->json_nl, h->json_chunk_cnt, h->json_ns_keys, h->json_ns_off,
-                    h->json_ph_keys, h->json_ph_off, h->json_err, h->json_ns_remap, h->json_ph_remap};
+                    h->json_ph_keys, h->json_ph_off, h->json_err, h->json_ns_remap, h->json_ph_remap, h->tiny_in_dev, h->tiny_out_dev};
     for (void* b : bufs) if (b) cudaFree(b);
+    if (h->tiny_in_host) cudaFreeHost(h->tiny_in_host);
+    if (h->tiny_out_host) cudaFreeHost(h->tiny_out_host);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto& pe : h->pass_ev) { cudaEventDestroy(pe.first); cudaEventDestroy(pe.second); }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
@@ -566,6 +575,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     }
     if (const char* ni = getenv("PTE_NO_INVERT")) h->no_invert = atoi(ni) != 0;
     if (const char* nd = getenv("PTE_NO_DEFER")) h->no_defer = atoi(nd) != 0;
+    if (const char* ty = getenv("PTE_TINY")) h->tiny_on = atoi(ty) != 0;
     if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
     if (const char* sc = getenv("PTE_SCATTER_CFG")) h->scatter_cfg = std::min(std::max(atoi(sc), 0), 3);
     if (const char* pm = getenv("PTE_PART_MIN")) h->part_min_events = (u64)atof(pm);
@@ -604,6 +614,13 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     CKC(prepare_partition(h));
     CKC(dev_alloc(h, &h->hist, (u64)kMaxPasses * kRadix));
     CKC(dev_alloc(h, &h->ctr, 1));
+    CKCU(cudaFuncSetAttribute(tiny_replay_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTinySmem));
+    {
+        const size_t in_bytes = (size_t)kTinyMax * (8 + 8 + 8 + 4 + 1 + 1), out_bytes = sizeof(Counters) + (size_t)kTinyMax * 5;
+        CKC(dev_alloc(h, &h->tiny_in_dev, in_bytes)); CKC(dev_alloc(h, &h->tiny_out_dev, out_bytes));
+        CKCU(cudaHostAlloc((void**)&h->tiny_in_host, in_bytes, cudaHostAllocDefault));
+        CKCU(cudaHostAlloc((void**)&h->tiny_out_host, out_bytes, cudaHostAllocDefault));
+    }
     CKC(alloc_event_buffers(h));
     CKC(dev_alloc(h, &h->d_counts_send, 4));
     CKCU(cudaMemsetAsync(h->ctr, 0, sizeof(Counters), h->stream));
@@ -649,17 +666,44 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
 
 // One batch of a live stream in ONE call: copy in, replay as the next PTE_RUN_CARRY batch, arrival index + event type of
 // the notifications out.  Same as pte_ingest + pte_run + pte_fetch(idx, type) with two host synchronisations less.
+static int tiny_unstage(pte_handle h);
 int pte_stream_batch(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv, const uint32_t* ns_id,
                      const uint8_t* phase, const uint8_t* type, uint64_t n, int flags, uint32_t* idx_out, uint8_t* type_out,
                      uint64_t cap, pte_stats* out) {
-    int rc = ingest_impl(h, uid_hi, uid_lo, rv, ns_id, phase, type, n, false);
-    if (rc) return rc;
+    int rc;
+    if (h && h->tiny_on && n && n <= kTinyMax && n <= h->max_events && (flags & PTE_RUN_DEDUPE) && uid_hi && uid_lo && rv && phase && type &&
+        (ns_id || !h->ns_filter_on)) {
+        // a small batch: packed in pinned memory, ONE copy to the device; the replay kernel spreads it over the columns
+        CK(h, cudaSetDevice(h->device));
+        u8* q = h->tiny_in_host;
+        memcpy(q, uid_hi, n * 8); q += n * 8;
+        memcpy(q, uid_lo, n * 8); q += n * 8;
+        memcpy(q, rv, n * 8); q += n * 8;
+        if (ns_id) memcpy(q, ns_id, n * 4); else memset(q, 0, n * 4);
+        q += n * 4;
+        memcpy(q, phase, n); q += n;
+        memcpy(q, type, n); q += n;
+        CK(h, cudaMemcpyAsync(h->tiny_in_dev, h->tiny_in_host, (size_t)(q - h->tiny_in_host), cudaMemcpyHostToDevice, h->stream));
+        h->tiny_staged = true;
+        h->ns_loaded = true;
+        h->n_events = n;
+        h->has_run = false;
+        h->batch_first_rv = rv[0];
+        h->batch_last_rv = rv[n - 1];
+    } else {
+        rc = ingest_impl(h, uid_hi, uid_lo, rv, ns_id, phase, type, n, false);
+        if (rc) return rc;
+    }
     pte_stats st;
     rc = pte_run(h, flags & ~PTE_RUN_BITMAP_ONLY, &st);      // synchronises the stream: the host columns are free again
-    if (rc) return rc;
+    if (rc) { tiny_unstage(h); return rc; }                  // (a batch refused before its replay still ends up in the columns)
     if (out) *out = st;
     if (st.n_emitted > cap) FAIL(h, PTE_ERR_CAPACITY, "buffers smaller than the emitted record count");
-    if (st.n_emitted && (idx_out || type_out)) {
+    if (st.n_emitted && h->tiny_result) {
+        const u8* r = h->tiny_out_host + sizeof(Counters);
+        if (idx_out) memcpy(idx_out, r, st.n_emitted * 4);
+        if (type_out) memcpy(type_out, r + st.n_emitted * 4, st.n_emitted);
+    } else if (st.n_emitted && (idx_out || type_out)) {
         if (idx_out) CK(h, cudaMemcpyAsync(idx_out, h->out_idx, st.n_emitted * 4, cudaMemcpyDeviceToHost, h->stream));
         if (type_out) CK(h, cudaMemcpyAsync(type_out, h->out_type, st.n_emitted, cudaMemcpyDeviceToHost, h->stream));
         CK(h, cudaStreamSynchronize(h->stream));
@@ -782,6 +826,23 @@ int pte_generate(pte_handle h, const pte_gen_params* p) {
     return PTE_OK;
 }
 
+// A batch that pte_stream_batch left in the packed staging buffer -> the column arrays (what the replay kernel of the
+// small-batch path does on its way; needed when the batch takes the bulk kernels or is not replayed at all).
+static int tiny_unstage(pte_handle h) {
+    if (!h->tiny_staged) return PTE_OK;
+    const u64 n = h->n_events;
+    cudaStream_t st = h->stream;
+    const u8* q = h->tiny_in_dev;
+    CK(h, cudaMemcpyAsync(h->uid_hi, q, n * 8, cudaMemcpyDeviceToDevice, st)); q += n * 8;
+    CK(h, cudaMemcpyAsync(h->uid_lo, q, n * 8, cudaMemcpyDeviceToDevice, st)); q += n * 8;
+    CK(h, cudaMemcpyAsync(h->rv, q, n * 8, cudaMemcpyDeviceToDevice, st)); q += n * 8;
+    CK(h, cudaMemcpyAsync(h->ns, q, n * 4, cudaMemcpyDeviceToDevice, st)); q += n * 4;
+    CK(h, cudaMemcpyAsync(h->phase, q, n, cudaMemcpyDeviceToDevice, st)); q += n;
+    CK(h, cudaMemcpyAsync(h->type, q, n, cudaMemcpyDeviceToDevice, st));
+    h->tiny_staged = false;
+    return PTE_OK;
+}
+
 int pte_run(pte_handle h, int flags, pte_stats* out) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     CK(h, cudaSetDevice(h->device));
@@ -805,13 +866,17 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     // large one-shot T-trace replays take the partition-first path (pte_partition.cuh); streams and short logs the sort path
     const bool use_part = dedupe && !carry && n && !h->force_sort && h->path_mode != 1 &&
                           (h->path_mode == 2 || n >= h->part_min_events);
+    // batches of a few thousand events: one launch does the whole replay (pte_tiny.cuh)
+    const bool use_tiny = h->tiny_on && dedupe && n && n <= kTinyMax && !use_part;
+    if (!use_tiny) { int rcu = tiny_unstage(h); if (rcu) return rcu; }     // the bulk kernels read the column arrays
+    h->tiny_result = false;
     if (fresh) {
         CK(h, cudaMemsetAsync(h->table, 0, (use_part ? (u64)kParts * h->part_slice : h->table_cap) * sizeof(Slot), st));
         if (carry) CK(h, cudaMemsetAsync(h->state_old, 0, h->table_cap, st));
         h->pods_total = 0;
     }
-    if (carry) CK(h, cudaMemcpyAsync(h->state_new, h->state_old, h->table_cap, cudaMemcpyDeviceToDevice, st));
-    CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
+    if (carry && !use_tiny) CK(h, cudaMemcpyAsync(h->state_new, h->state_old, h->table_cap, cudaMemcpyDeviceToDevice, st));
+    if (!use_tiny) CK(h, cudaMemsetAsync(h->ctr, 0, sizeof(Counters), st));
     const bool filtered = h->critical_only || h->ns_filter_on;
     InternArgs a;
     a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
@@ -820,7 +885,25 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     a.critical_only = h->critical_only; a.ctr = h->ctr; a.keep = h->keepmap; a.block_off = h->lookback;
     a.hist = h->hist; a.key_passes = (int)(h->L.key_bits + 7) / 8;
     const u64* n_surv_ptr = &h->ctr->n_survived;
-    if (use_part) {
+    if (use_tiny) {
+        TinyArgs t;
+        const u8* q = h->tiny_in_dev;
+        if (h->tiny_staged) {
+            t.src_hi = (const u64*)q; q += n * 8; t.src_lo = (const u64*)q; q += n * 8; t.src_rv = (const u64*)q; q += n * 8;
+            t.src_ns = (const u32*)q; q += n * 4; t.src_phase = q; q += n; t.src_type = q;
+        } else {
+            t.src_hi = h->uid_hi; t.src_lo = h->uid_lo; t.src_rv = h->rv; t.src_ns = h->ns; t.src_phase = h->phase; t.src_type = h->type;
+        }
+        t.uid_hi = h->uid_hi; t.uid_lo = h->uid_lo; t.rv = h->rv; t.ns = h->ns; t.phase = h->phase; t.type = h->type;
+        t.n = (u32)n; t.table = h->table; t.table_mask = (u32)(h->table_cap - 1);
+        t.ns_bitmap = h->ns_bitmap; t.ns_words = h->ns_words; t.ns_filter_on = h->ns_filter_on; t.critical_only = h->critical_only;
+        t.carry = carry ? 1 : 0; t.state = h->state_old; t.prev_rv = 0;
+        t.ctr = h->ctr; t.bitmap = h->bitmap; t.out_idx = h->out_idx; t.out_type = h->out_type; t.packed = h->tiny_out_dev;
+        tiny_replay_kernel<<<1, kTinyThreads, kTinySmem, st>>>(t);
+        CK(h, cudaGetLastError());
+        h->tiny_staged = false;          // the kernel has spread the batch over the column arrays
+        h->n_launches = 1;
+    } else if (use_part) {
         int rc = run_partitioned(h, a, filtered);
         if (rc) return rc;
     } else if (n && dedupe) {
@@ -846,14 +929,16 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         CK(h, cudaGetLastError());
         h->n_launches++;
     }
-    if (!use_part) CK(h, cudaEventRecord(h->ev[1], st));
+    if (!use_part && !use_tiny) CK(h, cudaEventRecord(h->ev[1], st));
     AssembleArgs as;
     as.n = n; as.bitmap = h->bitmap;
     as.rv = h->rv; as.ns = h->ns; as.phase = h->phase; as.type = h->type;
     as.ctr = h->ctr; as.lookback = h->lookback;
     as.out_idx = h->out_idx; as.out_rv = h->out_rv; as.out_ns = h->out_ns;
     as.out_phase = h->out_phase; as.out_type = h->out_type;
-    if (use_part) {
+    if (use_tiny) {
+        // one kernel: only the total is timed (every event record and every elapsed-time query costs the live loop a microsecond or two)
+    } else if (use_part) {
         // run_partitioned has filled the emit bitmap and recorded ev[1], ev[2]
     } else if (n && dedupe) {
         u64* sorted = nullptr;
@@ -919,9 +1004,11 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             h->n_launches++;
         }
     }
-    CK(h, cudaEventRecord(h->ev[3], st));
-    CK(h, cudaEventRecord(h->ev[4], st));
-    if (n) {
+    if (!use_tiny) {
+        CK(h, cudaEventRecord(h->ev[3], st));
+        CK(h, cudaEventRecord(h->ev[4], st));
+    }
+    if (n && !use_tiny) {
         const u64 tiles = (n + kAsmTile - 1) / kAsmTile;
         int grid = (int)std::min<u64>(tiles, (u64)h->num_sms * 8);
         bitmap_count_kernel<<<grid, 256, 0, st>>>(h->bitmap, n, h->lookback);
@@ -937,8 +1024,16 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         h->n_launches += 2;
     }
     CK(h, cudaEventRecord(h->ev[5], st));
-    CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-    CK(h, cudaStreamSynchronize(st));
+    if (use_tiny) {
+        // counters and notifications in one copy (at most n of them; how many is only known afterwards)
+        CK(h, cudaMemcpyAsync(h->tiny_out_host, h->tiny_out_dev, sizeof(Counters) + n * 5, cudaMemcpyDeviceToHost, st));
+        CK(h, cudaStreamSynchronize(st));
+        memcpy(&h->last, h->tiny_out_host, sizeof(Counters));
+        h->tiny_result = true;
+    } else {
+        CK(h, cudaMemcpyAsync(&h->last, h->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+        CK(h, cudaStreamSynchronize(st));
+    }
     if (dedupe) h->last.n_tombstones = h->last.n_del_survived;      // every DELETED survivor is a tombstone of the T-trace
     if (use_part && (h->last.flags & (kFlagTableFull | kFlagPendingFull | kFlagSegmentsFull)) && !(h->last.flags & kFlagBadEvent)) {
         // a partition's dictionary slice, the segment table or the pending list overflowed (hash imbalance, extreme
@@ -969,7 +1064,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
     }
     h->last_ordered = 1;
     h->pods_total += h->last.n_pods;
-    if (carry) { std::swap(h->state_old, h->state_new); h->stream_last_rv = n ? h->batch_last_rv : h->stream_last_rv; }
+    if (carry) { if (!use_tiny) std::swap(h->state_old, h->state_new); h->stream_last_rv = n ? h->batch_last_rv : h->stream_last_rv; }
     h->carry_valid = carry;
     h->has_run = true;
     h->cols_valid = !(flags & PTE_RUN_BITMAP_ONLY);
@@ -981,11 +1076,13 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         out->n_tombstones = h->last.n_tombstones; out->n_pods = h->pods_total;
         out->ordered = 1; out->n_launches = h->n_launches;
         cudaEventElapsedTime(&out->ms_total, h->ev[0], h->ev[5]);
-        cudaEventElapsedTime(&out->ms_intern, h->ev[0], h->ev[1]);
-        cudaEventElapsedTime(&out->ms_sort_key, h->ev[1], h->ev[2]);
-        cudaEventElapsedTime(&out->ms_diff, h->ev[2], h->ev[3]);
-        cudaEventElapsedTime(&out->ms_sort_order, h->ev[3], h->ev[4]);
-        cudaEventElapsedTime(&out->ms_assemble, h->ev[4], h->ev[5]);
+        if (!use_tiny) {
+            cudaEventElapsedTime(&out->ms_intern, h->ev[0], h->ev[1]);
+            cudaEventElapsedTime(&out->ms_sort_key, h->ev[1], h->ev[2]);
+            cudaEventElapsedTime(&out->ms_diff, h->ev[2], h->ev[3]);
+            cudaEventElapsedTime(&out->ms_sort_order, h->ev[3], h->ev[4]);
+            cudaEventElapsedTime(&out->ms_assemble, h->ev[4], h->ev[5]);
+        }
         float sum = 0;
         for (size_t i = 0; i < h->pass_ev_used; i++) {
             float ms = 0;

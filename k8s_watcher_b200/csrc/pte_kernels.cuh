@@ -165,7 +165,8 @@ static constexpr int kInternPerThread = 4;
 static constexpr int kInternTile = kInternThreads * kInternPerThread;
 
 // The reference's two predicates, on integer codes.
-__device__ __forceinline__ bool passes_filters(const InternArgs& a, u32 ty, u32 ph, u32 ns) {
+template <typename Args>
+__device__ __forceinline__ bool passes_filters(const Args& a, u32 ty, u32 ph, u32 ns) {
     // should_process_event, pod_watcher.py:209
     if (a.critical_only && ty != kTypeDeleted && ph != kPhNoStatus && ph != kPhFailed && ph != kPhSucceeded) return false;
     // namespace allow-list, pod_watcher.py:227
