@@ -109,6 +109,7 @@ struct pte_engine {
     u32 *bitmap = nullptr, *keepmap = nullptr;               // one emit / keep bit per arrival position
     u8 *state_old = nullptr, *state_new = nullptr;           // per dictionary slot: last known phase of the stream
     // small batches in one launch (pte_tiny.cuh): packed staging in pinned host memory and on the device
+    bool force_stage_timing = false;                         // PTE_STAGE_TIMING=1
     bool tiny_on = true;                                     // PTE_TINY=0: every batch takes the bulk kernels
     u8 *tiny_in_host = nullptr, *tiny_in_dev = nullptr;      // uid_hi | uid_lo | rv | ns | phase | type of one batch
     u8 *tiny_out_host = nullptr, *tiny_out_dev = nullptr;    // Counters | out_idx | out_type of one batch
@@ -162,6 +163,7 @@ struct pte_engine {
     u32 n_launches = 0, n_diff_rounds = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pass_ev;
     size_t pass_ev_used = 0;
+    bool stage_timing = true;                                // per-stage events: only for runs long enough for them not to matter (>= 2^20 events)
     // multi-GPU
     ncclComm_t comm = nullptr;
     int rank = 0, n_ranks = 1;
@@ -248,11 +250,11 @@ int sort_field(pte_engine* h, u64* src, u64* x, u64* y, const u64* n_ptr, u64 n_
             CK(h, cudaEventCreate(&e1));
             h->pass_ev.emplace_back(e0, e1);
         }
-        auto& pe = h->pass_ev[h->pass_ev_used++];
-        CK(h, cudaEventRecord(pe.first, h->stream));
+        auto& pe = h->pass_ev[h->pass_ev_used++];             // (counted in any case: pte_stats.n_passes)
+        if (h->stage_timing) CK(h, cudaEventRecord(pe.first, h->stream));
         int rc = launch_pass_cfg(h, a, b, n_ptr, n_upper, shift, mask, h->hist + p * kRadix);
         if (rc) return rc;
-        CK(h, cudaEventRecord(pe.second, h->stream));
+        if (h->stage_timing) CK(h, cudaEventRecord(pe.second, h->stream));
         if (p == 0) { a = x; b = y; } else std::swap(a, b);
     }
     *result = a;
@@ -576,6 +578,7 @@ int pte_create(int device, uint64_t max_events, uint64_t max_pods, pte_handle* o
     if (const char* ni = getenv("PTE_NO_INVERT")) h->no_invert = atoi(ni) != 0;
     if (const char* nd = getenv("PTE_NO_DEFER")) h->no_defer = atoi(nd) != 0;
     if (const char* ty = getenv("PTE_TINY")) h->tiny_on = atoi(ty) != 0;
+    if (const char* sg = getenv("PTE_STAGE_TIMING")) h->force_stage_timing = atoi(sg) != 0;
     if (const char* rb = getenv("PTE_DIFF_ROUND_MB")) h->diff_round_bytes = std::max(1, atoi(rb)) * (1ull << 20);
     if (const char* sc = getenv("PTE_SCATTER_CFG")) h->scatter_cfg = std::min(std::max(atoi(sc), 0), 3);
     if (const char* pm = getenv("PTE_PART_MIN")) h->part_min_events = (u64)atof(pm);
@@ -868,6 +871,9 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
                           (h->path_mode == 2 || n >= h->part_min_events);
     // batches of a few thousand events: one launch does the whole replay (pte_tiny.cuh)
     const bool use_tiny = h->tiny_on && dedupe && n && n <= kTinyMax && !use_part;
+    // every event record costs a short run a microsecond or two on the device and on the host: stages are timed from 2^20 events on
+    const bool stages = !use_tiny && (n >= (1ull << 20) || h->force_stage_timing || use_part);
+    h->stage_timing = stages;
     if (!use_tiny) { int rcu = tiny_unstage(h); if (rcu) return rcu; }     // the bulk kernels read the column arrays
     h->tiny_result = false;
     if (fresh) {
@@ -929,7 +935,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         CK(h, cudaGetLastError());
         h->n_launches++;
     }
-    if (!use_part && !use_tiny) CK(h, cudaEventRecord(h->ev[1], st));
+    if (!use_part && stages) CK(h, cudaEventRecord(h->ev[1], st));
     AssembleArgs as;
     as.n = n; as.bitmap = h->bitmap;
     as.rv = h->rv; as.ns = h->ns; as.phase = h->phase; as.type = h->type;
@@ -945,7 +951,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         int rc = sort_field(h, h->recA, h->recB, h->recC, n_surv_ptr, n, h->L.key_shift(),
                             h->L.key_shift() + h->L.key_bits, &sorted, /*hist_ready=*/true);
         if (rc) return rc;
-        CK(h, cudaEventRecord(h->ev[2], st));
+        if (stages) CK(h, cudaEventRecord(h->ev[2], st));
         const u64 per_cta = (u64)kDiffThreads * kDiffPerThread;
         int grid = (int)std::min<u64>((n + per_cta - 1) / per_cta, (u64)h->num_sms * 16);
         // polarity: flip the bits of the minority (emitted or suppressed), estimated from a sample.  Stream
@@ -996,7 +1002,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         }
     } else {
         // R-trace: every survivor is emitted; nothing to intern or sort
-        CK(h, cudaEventRecord(h->ev[2], st));
+        if (stages) CK(h, cudaEventRecord(h->ev[2], st));
         if (n) {
             int grid = (int)std::min<u64>((n / 4 + 255) / 256 + 1, (u64)h->num_sms * 16);
             filter_flag_kernel<<<grid, 256, 0, st>>>(a, h->bitmap);
@@ -1004,7 +1010,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             h->n_launches++;
         }
     }
-    if (!use_tiny) {
+    if (stages) {
         CK(h, cudaEventRecord(h->ev[3], st));
         CK(h, cudaEventRecord(h->ev[4], st));
     }
@@ -1076,7 +1082,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
         out->n_tombstones = h->last.n_tombstones; out->n_pods = h->pods_total;
         out->ordered = 1; out->n_launches = h->n_launches;
         cudaEventElapsedTime(&out->ms_total, h->ev[0], h->ev[5]);
-        if (!use_tiny) {
+        if (stages) {
             cudaEventElapsedTime(&out->ms_intern, h->ev[0], h->ev[1]);
             cudaEventElapsedTime(&out->ms_sort_key, h->ev[1], h->ev[2]);
             cudaEventElapsedTime(&out->ms_diff, h->ev[2], h->ev[3]);
@@ -1084,7 +1090,7 @@ int pte_run(pte_handle h, int flags, pte_stats* out) {
             cudaEventElapsedTime(&out->ms_assemble, h->ev[4], h->ev[5]);
         }
         float sum = 0;
-        for (size_t i = 0; i < h->pass_ev_used; i++) {
+        for (size_t i = 0; stages && i < h->pass_ev_used; i++) {
             float ms = 0;
             cudaEventElapsedTime(&ms, h->pass_ev[i].first, h->pass_ev[i].second);
             sum += ms;
