@@ -139,8 +139,10 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
  * the current log.  uid must be a 128-bit hex uid (dashes ignored); a missing resourceVersion becomes line
  * number + 1; status absent or null -> PTE_PH_NOSTATUS, phase absent or null -> PTE_PH_NULL.  Namespaces, and phase
  * strings other than the five well-known ones, are interned exactly on the device (ids / codes >= 7 in order of
- * first occurrence); pte_json_strings returns the dictionaries.  On a bad line: PTE_ERR_PARSE, *bad_line = its
- * 0-based number, and the log is left empty. */
+ * first occurrence); pte_json_strings returns the dictionaries.  JSON escape sequences in the five strings are decoded
+ * (\" \\ \/ \b \f \n \r \t, \uXXXX with surrogate pairs, as UTF-8): two spellings of one string are one string, and
+ * pte_json_strings returns the decoded bytes.  On a bad line (not one JSON container, type / uid / resourceVersion not
+ * of the form above, a broken escape): PTE_ERR_PARSE, *bad_line = its 0-based number, and the log is left empty. */
 int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line);
 
 /* Device time of the last pte_ingest_json (CUDA events on the engine stream, host <-> device copies excluded):
@@ -213,7 +215,10 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
 /* One batch of a live stream (the body of `for event in stream`, pod_watcher.py:266-269, for a micro-batch) in one call:
  * pte_ingest + pte_run(flags, normally PTE_RUN_DEDUPE | PTE_RUN_CARRY) + pte_fetch(idx, type), with one host
  * synchronisation instead of three.  idx_out / type_out (capacity cap) receive the arrival index and the event type of
- * every notification of the batch; *out the counts.  Afterwards the engine is in the state pte_run leaves it in. */
+ * every notification of the batch; *out the counts.  Afterwards the engine is in the state pte_run leaves it in.
+ * Batches of up to 4096 events are replayed by a single kernel launch (packed pinned staging in, one packed copy out;
+ * same results; PTE_TINY=0 in the environment of pte_create switches that path off); pte_stats then holds ms_total and
+ * n_launches = 1 only.  Stage times (ms_intern ...) are measured for runs of 2^20 events or more (PTE_STAGE_TIMING=1: always). */
 int pte_stream_batch(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
                      const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n, int flags,
                      uint32_t* idx_out, uint8_t* type_out, uint64_t cap, pte_stats* out);
