@@ -21,9 +21,12 @@ def uid_to_str(hi: int, lo: int) -> str:
     return "-".join((h[0:8], h[8:12], h[12:16], h[16:20], h[20:32]))
 
 
+_CANONICAL_UID = None
+
+
 def str_to_uid(uid: str):
-    """metadata.uid -> (hi, lo).  UUID-shaped strings map bijectively; anything else is
-    hashed to 128 bits (blake2b) -- callers that need exactness for such uids keep a dictionary."""
+    """metadata.uid -> (hi, lo) for UUID-shaped strings (32 hex digits, dashes ignored: bijective on the canonical
+    lower-case 8-4-4-4-12 form Kubernetes emits).  Anything else raises ValueError: such uids need a UidInterner."""
     s = uid.replace("-", "")
     if len(s) == 32:
         try:
@@ -31,6 +34,43 @@ def str_to_uid(uid: str):
             return v >> 64, v & 0xFFFFFFFFFFFFFFFF
         except ValueError:
             pass
-    import hashlib
-    v = int.from_bytes(hashlib.blake2b(uid.encode(), digest_size=16).digest(), "big")
-    return v >> 64, v & 0xFFFFFFFFFFFFFFFF
+    raise ValueError("metadata.uid %r is not a 128-bit hex uid" % (uid,))
+
+
+class UidInterner:
+    """EXACT metadata.uid -> 128-bit engine key for whatever strings arrive (the reference takes any string,
+    watcher/pod_watcher.py:164).
+
+    The canonical form Kubernetes emits (lower-case hex, 8-4-4-4-12) maps to its own 128-bit value.  Every other
+    string -- and the few canonical ones whose value falls into the reserved block ``hi == 2**64 - 1`` or is zero -- gets
+    the next number of the reserved block from a dictionary, so two different strings never share a key and one string
+    always gets the same key for as long as the interner lives (one per watch stream)."""
+
+    RESERVED_HI = 0xFFFFFFFFFFFFFFFF
+
+    def __init__(self):
+        import re
+        self._canonical = re.compile(r"[0-9a-f]{8}-[0-9a-f]{4}-[0-9a-f]{4}-[0-9a-f]{4}-[0-9a-f]{12}\Z")
+        self._ids = {}          # string -> lo of its reserved key
+        self._strings = []      # lo - 1 -> string
+
+    def key(self, uid: str):
+        if self._canonical.match(uid):
+            v = int(uid.replace("-", ""), 16)
+            hi, lo = v >> 64, v & 0xFFFFFFFFFFFFFFFF
+            if hi != self.RESERVED_HI and v != 0:
+                return hi, lo
+        lo = self._ids.get(uid)
+        if lo is None:
+            self._strings.append(uid)
+            lo = self._ids[uid] = len(self._strings)
+        return self.RESERVED_HI, lo
+
+    def string(self, hi: int, lo: int) -> str:
+        """The uid string of a key this interner handed out (or the canonical form of a direct one)."""
+        if int(hi) == self.RESERVED_HI and 0 < int(lo) <= len(self._strings):
+            return self._strings[int(lo) - 1]
+        return uid_to_str(hi, lo)
+
+    def __len__(self):
+        return len(self._strings)

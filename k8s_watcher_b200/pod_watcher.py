@@ -171,6 +171,7 @@ class PodWatcher:
         self._seq = 0                                # arrival number of the next live event (the stream's order key)
         self.max_pods = max_pods
         self._stream_namespaces: List[str] = []      # namespace dictionary shared by all batches of a stream
+        self._stream_uids = codes.UidInterner()      # uid string -> 128-bit key, shared by all batches of a stream
 
     # ---- configuration (pod_watcher.py:19-75) ---------------------------------
     def _load_environment_config(self) -> Dict[str, Any]:
@@ -391,7 +392,8 @@ class PodWatcher:
             return None
         # the stream's order key is the arrival number, as in the reference's loop (metadata.resource_version is
         # neither read upstream nor ordered across the initial list of a list+watch)
-        log = ReplayLog.from_events(self._pending, namespaces=self._stream_namespaces, seq_start=self._seq + 1)
+        log = ReplayLog.from_events(self._pending, namespaces=self._stream_namespaces, seq_start=self._seq + 1,
+                                    uids=self._stream_uids)
         self._seq += len(self._pending)
         self._pending = []
         self._last_flush = time.monotonic()

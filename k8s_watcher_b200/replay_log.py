@@ -30,6 +30,7 @@ class ReplayLog:
         # True: the rows are in the order the watcher received them and that IS the replay order (the reference's loop
         # knows no other; it never reads resourceVersion).  replay() then leaves the rv column on the host.
         self.arrival_ordered = False
+        self.uids: Optional[codes.UidInterner] = None      # set by from_events: maps keys of non-UUID uids back
 
     def __len__(self):
         return int(self.columns["rv"].shape[0])
@@ -60,12 +61,15 @@ class ReplayLog:
     # ---- construction -------------------------------------------------------
     @classmethod
     def from_events(cls, events: Iterable[Dict[str, Any]], namespaces: Optional[List[str]] = None,
-                    seq_start: Optional[int] = None) -> "ReplayLog":
+                    seq_start: Optional[int] = None, uids: Optional[codes.UidInterner] = None) -> "ReplayLog":
         """Intern a stream of ``{'type': str, 'object': V1Pod}`` dicts (pod_watcher.py:267-268).
         ``namespaces`` is an optional, growing id -> name list shared between the batches of one stream.
         ``seq_start``: order the events by arrival (``rv = seq_start + i``) instead of by their
-        ``metadata.resource_version`` -- what a live watch loop wants, see PodWatcher.flush."""
+        ``metadata.resource_version`` -- what a live watch loop wants, see PodWatcher.flush.
+        ``uids``: the stream's UidInterner (exact keys for uid strings of any form, stable across batches); a fresh one
+        per log otherwise."""
         events = list(events)
+        uids = uids if uids is not None else codes.UidInterner()
         n = len(events)
         cols = {name: np.zeros(n, dt) for name, dt in COLUMNS}
         shared = namespaces if namespaces is not None else []
@@ -79,7 +83,7 @@ class ReplayLog:
             if t not in codes.TYPE_CODE:
                 raise ValueError("event %d: type %r is not ADDED/MODIFIED/DELETED" % (i, t))
             md = pod.metadata
-            hi, lo = codes.str_to_uid(md.uid)
+            hi, lo = uids.key(md.uid)
             cols["uid_hi"][i], cols["uid_lo"][i] = hi, lo
             rvs = getattr(md, "resource_version", None)
             if seq_start is not None:
@@ -108,6 +112,7 @@ class ReplayLog:
             names[v] = k
         shared[:] = names
         log = cls(cols, names, phases, pods)
+        log.uids = uids
         log.arrival_ordered = seq_start is not None
         return log
 
@@ -136,7 +141,7 @@ class ReplayLog:
             return self._pods[i]
         c = self.columns
         code = int(c["phase"][i])
-        uid = codes.uid_to_str(c["uid_hi"][i], c["uid_lo"][i])
+        uid = self.uids.string(c["uid_hi"][i], c["uid_lo"][i]) if self.uids else codes.uid_to_str(c["uid_hi"][i], c["uid_lo"][i])
         md = _Attr(name="pod-" + uid[:13], namespace=self.namespaces[int(c["ns_id"][i])], uid=uid, labels=None,
                    annotations=None, creation_timestamp=None, resource_version=str(int(c["rv"][i])))
         status = None if code == codes.PH_NOSTATUS else _Attr(phase=self.phases[code], conditions=None,

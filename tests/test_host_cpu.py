@@ -78,7 +78,39 @@ def test_uid_string_round_trip():
     for hi, lo in ((1, 2), (0xFFFFFFFFFFFFFFFF, 0), (0x0123456789ABCDEF, 0xFEDCBA9876543210)):
         assert codes.str_to_uid(codes.uid_to_str(hi, lo)) == (hi, lo)
     assert codes.uid_to_str(0x0123456789ABCDEF, 0xFEDCBA9876543210) == "01234567-89ab-cdef-fedc-ba9876543210"
-    assert codes.str_to_uid("not-a-uuid") == codes.str_to_uid("not-a-uuid")
+    with pytest.raises(ValueError):
+        codes.str_to_uid("not-a-uuid")
+
+
+def test_uid_interner_is_exact_for_any_string():
+    """metadata.uid is whatever string arrives (pod_watcher.py:164): different strings never share a key, one string
+    always has the same key, canonical UUIDs keep their own value."""
+    u = codes.UidInterner()
+    canon = "01234567-89ab-cdef-fedc-ba9876543210"
+    assert u.key(canon) == (0x0123456789ABCDEF, 0xFEDCBA9876543210) and len(u) == 0
+    odd = ["not-a-uuid", "", canon.upper(), canon.replace("-", ""), "0123456-789ab-cdef-fedc-ba9876543210", canon + " ",
+           "ffffffff-ffff-ffff-0000-000000000001", "00000000-0000-0000-0000-000000000000", "pod/with/slashes", "é"]
+    keys = [u.key(s) for s in odd]
+    assert len(set(keys)) == len(odd) and all(hi == codes.UidInterner.RESERVED_HI and lo > 0 for hi, lo in keys)
+    assert [u.key(s) for s in odd] == keys and len(u) == len(odd)
+    assert [u.string(*k) for k in keys] == odd and u.string(*u.key(canon)) == canon
+    # the reserved block is not reachable by a canonical string: the one that would land there goes through the dictionary
+    assert u.key("ffffffff-ffff-ffff-0000-000000000002")[1] == len(odd) + 1
+
+
+def test_from_events_keeps_non_uuid_uids_apart_across_batches():
+    uids = codes.UidInterner()
+    names = []
+    a = [{"type": "ADDED", "object": fk.make_pod(1, "weird uid A", "default", "Running")},
+         {"type": "ADDED", "object": fk.make_pod(2, "weird uid B", "default", "Running")}]
+    b = [{"type": "MODIFIED", "object": fk.make_pod(2, "weird uid B", "default", "Failed")},
+         {"type": "ADDED", "object": fk.make_pod(3, codes.uid_to_str(7, 9), "default", "Running")}]
+    la = ReplayLog.from_events(a, namespaces=names, uids=uids)
+    lb = ReplayLog.from_events(b, namespaces=names, uids=uids)
+    ka = list(zip(la.columns["uid_hi"].tolist(), la.columns["uid_lo"].tolist()))
+    kb = list(zip(lb.columns["uid_hi"].tolist(), lb.columns["uid_lo"].tolist()))
+    assert ka[0] != ka[1] and kb[0] == ka[1] and kb[1] == (7, 9)
+    assert lb.uids.string(*kb[0]) == "weird uid B"
 
 
 def test_replay_log_from_events_round_trips_columns():
