@@ -224,8 +224,16 @@ __device__ __noinline__ u32 decode_small(const T& t, u32 s, u32 raw_len, char* b
 }
 
 // One line [p, end) of the text -> row i of the columns.
+static constexpr int kJsonThreads = 128;
+// the scanner's candidate queue of one thread: word k of entry e at base[(4 e + k) * blockDim + thread] (no bank conflicts)
+struct SmemQueue {
+    u32* base;
+    __device__ __forceinline__ void put(u32 e, u32 k, u32 v) { base[(4 * e + k) * kJsonThreads] = v; }
+    __device__ __forceinline__ u32 get(u32 e, u32 k) const { return base[(4 * e + k) * kJsonThreads]; }
+};
+
 template <typename T>
-__device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, u32 p, u32 end) {
+__device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, u32 p, u32 end, SmemQueue& q) {
     using namespace ptejson;
     u32 bad = kJsonOk;
     JsonFields f;
@@ -233,7 +241,7 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
     u32 type = 0, phase = kPhNoStatus, ns = 0;
     char buf[kJsonSmall];
     u32 n = 0;
-    if (!scan_line(t, p, end, f)) bad = kJsonMalformed;
+    if (!scan_line(t, p, end, f, q)) bad = kJsonMalformed;
     if (!bad) {
         const u32 s = span_start(f.type), len = span_len(f.type);
         bool ok = span_present(f.type);
@@ -283,14 +291,15 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
 
 // One thread per line, 32 consecutive lines per warp (handed out by ticket, so long and short lines even out); the
 // text comes straight from global memory in 32-byte blocks, the next block in flight while the current one is scanned.
-static constexpr int kJsonThreads = 128;
 #ifndef PTE_JSON_BLOCKS
 #define PTE_JSON_BLOCKS 6      // 8 (64 registers, spills) measured slower: 2.36 vs 2.30 ms per GB
 #endif
 
 __global__ void __launch_bounds__(kJsonThreads, PTE_JSON_BLOCKS) json_parse_kernel(JsonArgs a, u32* __restrict__ ticket) {
+    __shared__ u32 s_queue[ptejson::kQueueCap * 4 * kJsonThreads];
     const u32 lane = threadIdx.x & 31;
     const GlobalText t{a.text};
+    SmemQueue q{s_queue + threadIdx.x};
     for (;;) {
         u64 g0 = 0;
         if (lane == 0) g0 = (u64)atomicAdd(ticket, 1u) * 32;
@@ -300,7 +309,7 @@ __global__ void __launch_bounds__(kJsonThreads, PTE_JSON_BLOCKS) json_parse_kern
         if (li < a.n_lines) {
             const u32 p = li ? (u32)a.nl[li - 1] + 1u : 0u;
             const u32 end = li < a.n_nl ? (u32)a.nl[li] : (u32)a.len;
-            json_line(a, t, li, p, end);
+            json_line(a, t, li, p, end, q);
         }
         __syncwarp();
     }

@@ -93,22 +93,28 @@ PTE_JS_HD constexpr u64 low_bytes(int n) { return n >= 8 ? ~0ull : ((1ull << (8 
 // one who did would simply not be seen.
 template <typename T>
 PTE_JS_HD u32 key_meaning(const T& t, u32 s, u32 len, u32 ctx) {
-    if (len < 3 || len > 15) return W_NONE;
-    const u64 k = t.load8(s);
+    // the length alone rules most keys out (name, labels, annotations, spec, kind ...): no byte of those is looked at
+    u32 w = W_NONE;
+    u64 want = 0;
     if (ctx == C_ROOT) {
-        if (len == 4 && (k & low_bytes(4)) == word_of("type", 4)) return W_TYPE;
-        if (len == 6 && (k & low_bytes(6)) == word_of("object", 6)) return W_OBJECT;
+        if (len == 4) { w = W_TYPE; want = word_of("type", 4); }
+        else if (len == 6) { w = W_OBJECT; want = word_of("object", 6); }
     } else if (ctx == C_OBJECT) {
-        if (len == 8 && k == word_of("metadata", 8)) return W_META;
-        if (len == 6 && (k & low_bytes(6)) == word_of("status", 6)) return W_STATUS;
+        if (len == 8) { w = W_META; want = word_of("metadata", 8); }
+        else if (len == 6) { w = W_STATUS; want = word_of("status", 6); }
     } else if (ctx == C_META) {
-        if (len == 3 && (k & low_bytes(3)) == word_of("uid", 3)) return W_UID;
-        if (len == 9 && k == word_of("namespac", 8) && t[s + 8] == 'e') return W_NS;
-        if (len == 15 && k == word_of("resource", 8) && (t.load8(s + 8) & low_bytes(7)) == word_of("Version", 7)) return W_RV;
+        if (len == 3) { w = W_UID; want = word_of("uid", 3); }
+        else if (len == 9) { w = W_NS; want = word_of("namespac", 8); }
+        else if (len == 15) { w = W_RV; want = word_of("resource", 8); }
     } else if (ctx == C_STATUS) {
-        if (len == 5 && (k & low_bytes(5)) == word_of("phase", 5)) return W_PHASE;
+        if (len == 5) { w = W_PHASE; want = word_of("phase", 5); }
     }
-    return W_NONE;
+    if (w == W_NONE) return W_NONE;
+    const u64 mask = len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
+    if ((t.load8(s) & mask) != want) return W_NONE;
+    if (w == W_NS && t[s + 8] != 'e') return W_NONE;
+    if (w == W_RV && (t.load8(s + 8) & low_bytes(7)) != word_of("Version", 7)) return W_NONE;
+    return w;
 }
 
 PTE_JS_HD void set_field(Fields& f, u32 w, Span sp) {
@@ -124,8 +130,34 @@ PTE_JS_HD void set_field(Fields& f, u32 w, Span sp) {
 // Semantics of the fields: a key counts where the reference would read it -- root.type, root.object.metadata.{uid,
 // namespace,resourceVersion}, root.object.status.phase, each container reached through exactly that key; a value that
 // is not a string leaves the field absent; of duplicate keys the last one wins (as in json.loads).
-template <typename T>
-PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
+// Candidate colons wait in a small per-thread queue (QS: q.put(entry, word, value) / q.get(entry, word); shared memory
+// on the device) until the line is through, or the queue is full: looking at them right away means that in every block
+// some lane of the warp drags the other 31 through the key comparison and the value look-up.  An entry is four words:
+// where the key string starts, where the colon is, (key length | meaning of the container << 4 | distance from the colon
+// to the next opening quote << 8, all ones = none seen), and where that string closes (kNever = not seen).
+static constexpr u32 kQueueCap = 12, kNoDelta = 0xFFFFFFu;
+
+template <typename T, typename QS>
+PTE_JS_HD void flush_queue(const T& t, QS& q, u32& n_q, Fields& f) {
+    for (u32 e = 0; e < n_q; e++) {
+        const u32 ks1 = q.get(e, 0), pos = q.get(e, 1), meta = q.get(e, 2), q_close = q.get(e, 3);
+        const u32 wv = key_meaning(t, ks1, meta & 15u, (meta >> 4) & 15u);
+        if (wv == W_NONE || wv >= W_OBJECT) continue;
+        Span sp = 0;                                    // a later duplicate wins, string or not
+        const u32 delta = meta >> 8;
+        if (delta != kNoDelta && q_close != ~0u) {
+            const u32 q_open = pos + delta;
+            bool adjacent = true;                       // the string must BE the value: nothing but whitespace after the colon
+            for (u32 x = pos + 1; x < q_open; x++) adjacent = adjacent && is_ws(t[x]);
+            if (adjacent) sp = make_span(q_open + 1, q_close - q_open - 1);
+        }
+        set_field(f, wv, sp);
+    }
+    n_q = 0;
+}
+
+template <typename T, typename QS>
+PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f, QS& q) {
     f.type = f.uid = f.ns = f.rv = f.phase = 0;
     f.has_status = false;
     while (p < end && is_ws(t[p])) p++;
@@ -133,8 +165,9 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
     { const char c = t[p]; if (c != '{' && c != '[') return false; }
 
     const u32 kNever = ~0u;
-    u32 depth = 0, ctxs = 0, pend = W_NONE;
-    u32 pend_q = 0, last_open_q = kNever, last_close_q = kNever;
+    u32 depth = 0, ctxs = 0, n_q = 0;
+    u32 pend = 0, pend_e = 0, pend_q = 0;            // pend: 0 nothing, 1 entry pend_e waits for its opening quote, 2 for the closing one (opened at pend_q)
+    u32 last_open_q = kNever, last_close_q = kNever;
     bool in_str = false, esc_carry = false, bad = false;
 
     u32 w[8];
@@ -177,15 +210,19 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
         in_str = (s >> 31) != 0;
         const u32 openq = Q & s, closeq = Q & ~s;
 
-        // a field's value string opened earlier (at pend_q) and not closed yet: the next quote behind pend_q closes it
-        if (pend != W_NONE && Q) {
+        // the value of the last queued candidate: its opening quote, then its closing quote, wherever they turn up
+        if (pend != 0 && Q) {
             u32 m = Q;
-            if (pend_q >= blk) m = pend_q - blk >= 32 ? 0u : (m & ~((2u << (pend_q - blk)) - 1u));
-            if (m) {
-                const u32 e = blk + ctz32(m);
-                set_field(f, pend, make_span(pend_q + 1, e - pend_q - 1));
-                pend = W_NONE;
+            if (pend == 1 && openq) {
+                const u32 o = ctz32(openq);
+                const u32 colon = q.get(pend_e, 1);
+                const u32 delta = blk + o - colon;
+                q.put(pend_e, 2, (q.get(pend_e, 2) & 0xFFu) | ((delta < kNoDelta ? delta : kNoDelta) << 8));
+                pend = delta < kNoDelta ? 2u : 0u;
+                pend_q = blk + o;
+                m = o == 31 ? 0u : (Q & ~((2u << o) - 1u));
             }
+            if (pend == 2 && m) { q.put(pend_e, 3, blk + ctz32(m)); pend = 0; }
         }
 
         // Brackets outside strings are walked one by one (they carry the nesting and say what a container means); colons
@@ -248,33 +285,29 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
             const u32 i = ctz32(cand);
             const u32 bit = 1u << i;
             cand &= cand - 1;
-            const u32 pos = blk + i;
             const u32 ctx = (cand_root & bit) ? (u32)C_ROOT : (cand_meta & bit) ? (u32)C_META : (u32)C_STATUS;
-            // the key: the last complete string in front of this colon
+            // the key: the last complete string in front of this colon; only its length is looked at here
             const u32 below = bit - 1u;
             const u32 ks = (openq & below) ? blk + top32(openq & below) : last_open_q;
             const u32 ke = (closeq & below) ? blk + top32(closeq & below) : last_close_q;
-            if (ks != kNever && ke != kNever && ke > ks) {
-                const u32 wv = key_meaning(t, ks + 1, ke - ks - 1, ctx);
-                if (wv != W_NONE && wv < W_OBJECT) {
-                    set_field(f, wv, 0);                 // a later duplicate wins, string or not
-                    pend = W_NONE;
-                    u32 q = pos + 1;
-                    char c = q < end ? t[q] : '\0';
-                    while (is_ws(c)) { q++; c = q < end ? t[q] : '\0'; }
-                    if (c == '"') {
-                        pend = wv; pend_q = q;
-                        if (q - blk < 32) {
-                            const u32 m = Q & ~((2u << (q - blk)) - 1u);
-                            if (m) {
-                                const u32 e = blk + ctz32(m);
-                                set_field(f, wv, make_span(q + 1, e - q - 1));
-                                pend = W_NONE;
-                            }
-                        }
-                    }
-                }
+            if (ks == kNever || ke == kNever || ke <= ks) continue;
+            const u32 len = ke - ks - 1;
+            const bool maybe = ctx == C_ROOT ? len == 4 : (ctx == C_META ? (len == 3 || len == 9 || len == 15) : len == 5);
+            if (!maybe) continue;
+            if (n_q == kQueueCap) flush_queue(t, q, n_q, f);
+            // the string that follows (if it is the value is checked when the entry is looked at)
+            u32 delta = kNoDelta, q_close = ~0u;
+            pend = 1; pend_e = n_q;
+            const u32 oq = i == 31 ? 0u : (openq & ~((2u << i) - 1u));
+            if (oq) {
+                const u32 o = ctz32(oq);
+                delta = o - i;
+                pend = 2; pend_q = blk + o;
+                const u32 cq = o == 31 ? 0u : (Q & ~((2u << o) - 1u));
+                if (cq) { q_close = blk + ctz32(cq); pend = 0; }
             }
+            q.put(n_q, 0, ks + 1); q.put(n_q, 1, blk + i); q.put(n_q, 2, len | (ctx << 4) | (delta << 8)); q.put(n_q, 3, q_close);
+            n_q++;
         }
         if (openq) last_open_q = blk + top32(openq);
         if (closeq) last_close_q = blk + top32(closeq);
@@ -283,7 +316,8 @@ PTE_JS_HD bool scan_line(const T& t, u32 p, u32 end, Fields& f) {
             for (int k = 0; k < 8; k++) w[k] = nx[k];
         }
     }
-    return depth == 0 && !in_str && !bad && pend == W_NONE;
+    flush_queue(t, q, n_q, f);
+    return depth == 0 && !in_str && !bad;
 }
 
 // ---- escape sequences -------------------------------------------------------------------------------------

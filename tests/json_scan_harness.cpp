@@ -13,7 +13,12 @@ struct HostText {
 // out: for each of type, uid, ns, rv, phase: start, length (or -1, -1 when absent); then has_status.  Returns 1 when the line is accepted.
 extern "C" int scan_line_host(const char* text, unsigned long long p, unsigned long long end, long long* out) {
     ptejson::Fields f;
-    const bool ok = ptejson::scan_line(HostText{text}, (unsigned int)p, (unsigned int)end, f);
+    struct HostQueue {
+        unsigned int w[ptejson::kQueueCap][4];
+        void put(unsigned int e, unsigned int k, unsigned int v) { w[e][k] = v; }
+        unsigned int get(unsigned int e, unsigned int k) const { return w[e][k]; }
+    } q;
+    const bool ok = ptejson::scan_line(HostText{text}, (unsigned int)p, (unsigned int)end, f, q);
     const ptejson::Span sp[5] = {f.type, f.uid, f.ns, f.rv, f.phase};
     for (int k = 0; k < 5; k++) {
         out[2 * k] = ptejson::span_present(sp[k]) ? (long long)ptejson::span_start(sp[k]) : -1;

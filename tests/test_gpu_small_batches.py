@@ -162,3 +162,24 @@ def test_dictionary_rebuild_inside_a_stream_of_small_batches(mode):
             got.append(out.idx.astype(np.int64) + lo)
         assert st["n_rebuilds"] > 0
     assert np.array_equal(np.concatenate(got), want.astype(np.int64))
+
+
+@pytest.mark.parametrize("env", list(FILTERS))
+def test_small_unordered_log_replays_in_rv_order(mode, env):
+    """A short log that is not in resourceVersion order is pre-sorted on the device whichever path replays it; the
+    engine's copy of the log stays as it was handed over."""
+    n, pods = 3000, 120
+    flt = FILTERS[env]
+    cols = c_oracle.generate(SEED + 11, n, pods, dist=1, p_del=0.07, p_nostatus=0.03, p_null=0.03)
+    perm = np.random.default_rng(6).permutation(n)
+    shuf = {k: v[perm] for k, v in cols.items()}
+    want, ost, _ = c_oracle.replay(cols, critical_only=flt["critical_only"], ns_allow=flt["ns_allow"], pods_hint=pods)
+    with PhaseTransitionEngine(4096, pods) as e:
+        e.set_filters(flt["ns_allow"], critical_only=flt["critical_only"])
+        e.ingest(shuf)
+        st = e.run(dedupe=True)
+        assert st["ordered"] == 0 and st["n_emitted"] == ost["n_emitted"]
+        got = e.fetch(columns=("idx",)).idx.astype(np.int64)
+        assert np.array_equal(perm[got], want.astype(np.int64))
+        back = e.read_log()
+        assert all(np.array_equal(back[k], shuf[k]) for k in shuf)

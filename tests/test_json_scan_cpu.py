@@ -97,6 +97,14 @@ EDGE = [
     b'{"type":"ADDED","object":{"metadata":{"uid":                                             "far"}}}',
     b'{"type":"ADDED","object":{"metadata":{"labels":{"a":{"b":{"c":{"d":{"e":[[[[{"uid":"deep"}]]]]}}}}},"uid":"shallow"}}}',
     b'{"type":"ADDED","object":{"metadata":{"uid":"u"},"status":{"phase":"Running","conditions":[{"type":"Ready","phase":"no"}]}}}',
+    # more look-alike keys than the scanner's candidate queue holds (12): keys of the lengths it looks for, before, between and after the real ones
+    ('{"type":"ADDED","object":{"metadata":{' + ",".join('"k%02d":"v%d"' % (k, k) for k in range(30)) + ',"uid":"u-mid",'
+     + ",".join('"z%02d":%d' % (k, k) for k in range(30)) + ',"namespace":"ns-late","uid":"u-last"},"status":{'
+     + ",".join('"p%04d":"x"' % k for k in range(20)) + ',"phase":"Running"}}}').encode(),
+    b'{"type":"ADDED","object":{"metadata":{"uid":5,"namespace":"x","resourceVersion":null},"status":{"phase":7,"other":"Running"}}}',
+    b'{"type":"ADDED","object":{"metadata":{"uid":"first","uid":7,"namespace":"n1","namespace":"n2"}}}',
+    b'{"type":"ADDED","object":{"metadata":{"uid":null}},"type":"DELETED"}',
+    b'{"type" :   "MODIFIED"  ,"object":{"metadata":{"uid"\t:\t"tabbed","namespace":' + b" " * 70 + b'"after-seventy-spaces"}}}',
     b'{}', b'[]', b'{"type":""}', b'{"type":"ADDED","object":{"metadata":{"uid":""}}}',
     '{"type":"ADDED","object":{"metadata":{"uid":"u","namespace":"é中\U0001f600"}}}'.encode(),
 ]
