@@ -95,7 +95,9 @@ __device__ __forceinline__ ulonglong2 ld_slot(const Slot* p, u64 pol) {
 #define PTE_PROBE_LINE 1
 #endif
 __device__ __forceinline__ u32 probe_slot(u32 home, u32 p, u32 mask) {
-#if PTE_PROBE_LINE
+#if PTE_PROBE_LINE == 2      // experiment: runs confined to a 64-byte half line (with PTE_SLOT_LD=1: 64-byte L2 fetches)
+    return ((((home >> 2) + (p >> 2)) << 2) | ((home + p) & 3u)) & mask;
+#elif PTE_PROBE_LINE
     return ((((home >> 3) + (p >> 3)) << 3) | ((home + p) & 7u)) & mask;
 #else
     return (home + p) & mask;
@@ -103,7 +105,9 @@ __device__ __forceinline__ u32 probe_slot(u32 home, u32 p, u32 mask) {
 }
 // the same sequence, stepped: slot p from slot p-1 (needs no copy of `home` in a register)
 __device__ __forceinline__ u32 probe_next(u32 sl, u32 p, u32 mask) {
-#if PTE_PROBE_LINE
+#if PTE_PROBE_LINE == 2
+    return (((sl & ~3u) + ((p & 3u) == 0 ? 4u : 0u)) | ((sl + 1) & 3u)) & mask;
+#elif PTE_PROBE_LINE
     return (((sl & ~7u) + ((p & 7u) == 0 ? 8u : 0u)) | ((sl + 1) & 7u)) & mask;
 #else
     return (sl + 1) & mask;
