@@ -123,10 +123,11 @@ __device__ __forceinline__ ulonglong2 ld_slot_cg(const Slot* p, u64 pol) {
     return v;
 }
 
+// p0: how many slots of the run have been looked at already (sl is slot p0 of the run, v its content)
 template <bool CG = false>
 __device__ __forceinline__ u32 intern_uid(Slot* __restrict__ table, u32 mask, u64 hi, u64 lo, u32 sl, ulonglong2 v,
-                                          u32& inserted, u32* __restrict__ flags, u64 pol) {
-    for (int p = 0; p < kMaxProbe; ++p) {
+                                          u32& inserted, u32* __restrict__ flags, u64 pol, int p0 = 0) {
+    for (int p = p0; p < kMaxProbe; ++p) {
         if (v.x == 0 || v.y == 0) {
             ulonglong2 old = cas128(table + sl, 0, 0, hi, lo);
             if (old.x == 0 && old.y == 0) { inserted++; return sl; }
@@ -189,7 +190,10 @@ __device__ __forceinline__ bool passes_filters(const Args& a, u32 ty, u32 ph, u3
 //                    8192-event block; survivors are compacted in arrival order behind that offset.  No
 //                    ticket and no look-back: the blocks are independent.
 // (Interning in several rounds over L2-sized slices of the dictionary was tried and is slower: probes
-//  that hit L2 only halve the kernel, and every round has to re-read the uid columns.)
+//  that hit L2 only halve the kernel, and every round has to re-read the uid columns.
+//  Advancing the probe runs of a thread's four events together, so that second and third probes overlap, was tried
+//  too -- the dictionary's load costs 2.6 ms of the kernel, profiles/r02_yardsticks/table_load_sweep.txt -- and is 2-4 x
+//  slower: all lanes wait for the longest run of 128 events, and at 48 registers the extra state spills.)
 #ifndef PTE_INTERN_BLOCKS
 #define PTE_INTERN_BLOCKS 5      // measured on B200: 3/4/5/6 CTAs per SM -> 29.1/24.7/23.7/28.3 ms (6 spills too much)
 #endif
