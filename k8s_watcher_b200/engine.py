@@ -116,6 +116,7 @@ class PhaseTransitionEngine:
         self._h = C.c_void_p()
         _abi.check(L.pte_create(int(device), int(max_events), int(max_pods), C.byref(self._h)))
         self._L = L
+        self._stream_batch_fn = None
         self.max_events, self.max_pods, self.device = int(max_events), int(max_pods) or int(max_events), int(device)
         self.last_stats: Optional[Dict[str, float]] = None
 
@@ -303,10 +304,14 @@ class PhaseTransitionEngine:
         idx, ty = np.empty(n, np.uint32), np.empty(n, np.uint8)
         st = PteStats()
         flags = (1 if dedupe else 0) | (2 if carry and dedupe else 0)
-        self._ck(self._L.pte_stream_batch(
-            self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64), _ptr(c["rv"], C.c_uint64),
-            _ptr(c["ns_id"], C.c_uint32), _ptr(c["phase"], C.c_uint8), _ptr(c["type"], C.c_uint8), n, flags,
-            _ptr(idx, C.c_uint32), _ptr(ty, C.c_uint8), n, C.byref(st)))
+        # the live loop calls this once per batch: plain addresses instead of eight typed ctypes pointers (3.5 us each)
+        f = self._stream_batch_fn
+        if f is None:
+            f = self._stream_batch_fn = self._L["pte_stream_batch"]
+            f.restype = C.c_int
+            f.argtypes = [C.c_void_p] * 7 + [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(PteStats)]
+        self._ck(f(self._h, c["uid_hi"].ctypes.data, c["uid_lo"].ctypes.data, c["rv"].ctypes.data, c["ns_id"].ctypes.data,
+                   c["phase"].ctypes.data, c["type"].ctypes.data, n, flags, idx.ctypes.data, ty.ctypes.data, n, C.byref(st)))
         self.last_stats = st.as_dict()
         k = int(st.n_emitted)
         z = np.empty(0, np.uint64)
