@@ -183,3 +183,17 @@ def test_small_unordered_log_replays_in_rv_order(mode, env):
         assert np.array_equal(perm[got], want.astype(np.int64))
         back = e.read_log()
         assert all(np.array_equal(back[k], shuf[k]) for k in shuf)
+
+
+@pytest.mark.parametrize("tail", [1, 1000, 4096])
+def test_pipelined_replay_whose_last_chunk_is_small(mode, tail):
+    """pte_replay_pipelined cuts the log into carried chunks; a short last chunk takes the one-launch path."""
+    n, pods = 3 * 8192 + tail, 400
+    cols = c_oracle.generate(SEED + 13, n, pods, dist=1, p_del=0.06)
+    want, _, _ = c_oracle.replay(cols, pods_hint=pods)
+    with PhaseTransitionEngine(n, pods) as e:
+        for with_rv in (True, False):
+            words, st = e.replay_pipelined(cols, chunk_events=8192, with_rv=with_rv)
+            bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n]
+            assert np.array_equal(np.nonzero(bits)[0].astype(np.uint64), want), with_rv
+            assert st["n_emitted"] == len(want)
