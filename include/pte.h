@@ -145,6 +145,13 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
  * of the form above, a broken escape): PTE_ERR_PARSE, *bad_line = its 0-based number, and the log is left empty. */
 int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line);
 
+/* Raw watch text as a STREAM (the body of `for event in w.stream(...)`, pod_watcher.py:264-269, fed from the wire in pieces):
+ * with on != 0 every following pte_ingest_json is the next batch of one stream -- rows are numbered by arrival across the
+ * batches (that number is the order key; metadata.resourceVersion is not read, as in the reference's loop), and a
+ * namespace or phase string keeps the id / code it got when the stream first showed it, so PTE_RUN_CARRY compares like with
+ * like and pte_json_strings returns the stream's dictionaries so far.  Each call (on or off) starts afresh. */
+int pte_json_stream(pte_handle h, int on);
+
 /* Device time of the last pte_ingest_json (CUDA events on the engine stream, host <-> device copies excluded):
  * the line index (count, scan, list of newlines) and the scanner kernel; text_bytes = size of that log. */
 int pte_json_timing(pte_handle h, float* ms_index, float* ms_parse, uint64_t* text_bytes);

@@ -58,6 +58,7 @@ SYMBOLS = {
     "pte_ingest_json": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, _u64p, _u64p]),
     "pte_payload_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), _u64p]),
     "pte_json_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), _u64p]),
+    "pte_json_stream": (C.c_int, [C.c_void_p, C.c_int]),
     "pte_json_strings": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_uint64, _u32p, C.c_uint32, _u32p]),
     "pte_generate": (C.c_int, [C.c_void_p, C.POINTER(PteGenParams)]),
     "pte_generate_host": (C.c_int, [C.POINTER(PteGenParams), _u64p, _u64p, _u64p, _u32p, _u8p, _u8p]),

@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace {
@@ -129,6 +130,9 @@ struct pte_engine {
     u64* json_ns_keys = nullptr; u32* json_ns_off = nullptr; u64* json_ph_keys = nullptr; u32* json_ph_off = nullptr;
     u32 *json_err = nullptr, *json_ns_remap = nullptr; u8* json_ph_remap = nullptr;
     std::vector<std::string> json_names[2];                  // [0] namespaces by ns_id, [1] phase strings for codes >= 7
+    // pte_json_stream: the logs ingested are the batches of ONE stream -- ids and codes of names persist, rows are numbered by arrival
+    bool json_stream = false; u64 json_seq = 0;
+    std::unordered_map<std::string, u32> json_ids[2];
     u64* d_minmax = nullptr;
     float ms_payload = 0.f; u64 payload_bytes = 0;            // device time of the last payload_write_kernel
     float ms_json[2] = {0.f, 0.f}; u64 json_bytes = 0;        // device times of the last pte_ingest_json
@@ -1350,7 +1354,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
     h->has_run = false;
-    h->json_names[0].clear(); h->json_names[1].clear();
+    if (!h->json_stream) { h->json_names[0].clear(); h->json_names[1].clear(); }
     if (len == 0) { h->n_events = 0; return PTE_OK; }
     int rc;
     if ((rc = grow(h, &h->json_text, &h->json_text_cap, len + 64))) return rc;
@@ -1396,6 +1400,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     a.ns_dict = StrDict{h->json_ns_keys, h->json_ns_off, kJsonNsSlots - 1};
     a.phase_dict = StrDict{h->json_ph_keys, h->json_ph_off, kJsonPhSlots - 1};
     a.err = h->json_err;
+    a.arrival_order = h->json_stream ? 1 : 0; a.arrival_base = h->json_seq;
     grid = (int)std::min<u64>((n_lines + kJsonThreads - 1) / kJsonThreads, (u64)h->num_sms * 8);
     CK(h, cudaEventRecord(h->ev[1], st));
     json_parse_kernel<<<grid, kJsonThreads, 0, st>>>(a, h->json_err + 2);
@@ -1419,7 +1424,8 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
         FAIL(h, PTE_ERR_PARSE, std::string("watch log line ") + std::to_string(err[1]) + ": " + why[std::min<u32>(err[0], 7)]);
     }
     // 3. dictionary slots -> dense ids in order of first occurrence (deterministic), names kept for the host
-    auto build = [&](const std::vector<u64>& keys, const std::vector<u32>& offs, std::vector<std::string>& names, std::vector<u32>& remap) {
+    auto build = [&](const std::vector<u64>& keys, const std::vector<u32>& offs, std::vector<std::string>& names, std::vector<u32>& remap,
+                     std::unordered_map<std::string, u32>& ids) {
         std::vector<std::pair<u32, u32>> occ;      // (first offset, slot)
         for (u32 sl = 0; sl < keys.size(); sl++) if (keys[sl]) occ.emplace_back(offs[sl], sl);
         std::sort(occ.begin(), occ.end());
@@ -1430,13 +1436,16 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
             const HostJsonText ht{text};
             ptejson::Unescape<HostJsonText> u(ht, occ[id].first);
             for (u32 k = 0; k < l; k++) name.push_back((char)u.next());
-            names.push_back(std::move(name));
-            remap[sl] = id;
+            if (!h->json_stream) { names.push_back(std::move(name)); remap[sl] = id; continue; }
+            // stream: a name keeps the id it got when the stream first saw it
+            auto it = ids.find(name);
+            if (it == ids.end()) { it = ids.emplace(name, (u32)names.size()).first; names.push_back(std::move(name)); }
+            remap[sl] = it->second;
         }
     };
     std::vector<u32> nremap, premap32;
-    build(nk, no, h->json_names[0], nremap);
-    build(pk, po, h->json_names[1], premap32);
+    build(nk, no, h->json_names[0], nremap, h->json_ids[0]);
+    build(pk, po, h->json_names[1], premap32, h->json_ids[1]);
     if (h->json_names[1].size() > kPhMax - 6) {
         h->n_events = 0;
         FAIL(h, PTE_ERR_PARSE, "more than 56 distinct phase strings besides the five well-known ones");
@@ -1457,7 +1466,16 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     cudaEventElapsedTime(&h->ms_json[0], h->ev[0], h->ev[1]);       // line index (count, scan, list) + dictionary set-up
     cudaEventElapsedTime(&h->ms_json[1], h->ev[1], h->ev[2]);       // json_parse_kernel
     h->json_bytes = len;
+    if (h->json_stream) h->json_seq += n_lines;
     if (n_events) *n_events = n_lines;
+    return PTE_OK;
+}
+
+int pte_json_stream(pte_handle h, int on) {
+    if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
+    h->json_stream = on != 0;
+    h->json_seq = 0;
+    for (int k = 0; k < 2; k++) { h->json_names[k].clear(); h->json_ids[k].clear(); }
     return PTE_OK;
 }
 

@@ -153,6 +153,7 @@ struct JsonArgs {
     u64* uid_hi; u64* uid_lo; u64* rv; u32* ns; u8* phase; u8* type;
     StrDict ns_dict, phase_dict;
     u32* err;          // [0] worst error code, [1] (via atomicMin) first bad line + 1
+    int arrival_order; u64 arrival_base;   // stream mode: row i gets the order key arrival_base + i + 1, resourceVersion is not read
 };
 
 // ---- the five fields -> codes -------------------------------------------------------------------------
@@ -262,7 +263,8 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
         } else ok = ok && parse_uid(t, s, len, hi, lo);
         if (!bad && !ok) bad = kJsonBadUid;
     }
-    if (!bad && span_present(f.rv)) {
+    if (a.arrival_order) rv = a.arrival_base + i + 1;      // the reference's loop knows no other order (it never reads resourceVersion)
+    else if (!bad && span_present(f.rv)) {
         const u32 s = span_start(f.rv), len = span_len(f.rv);
         bool ok;
         if (has_backslash(t, s, len)) {

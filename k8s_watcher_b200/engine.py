@@ -176,6 +176,11 @@ class PhaseTransitionEngine:
         self._ck(self._L.pte_payload_timing(self._h, C.byref(a), C.byref(n)))
         return {"ms_write": a.value, "body_bytes": int(n.value)}
 
+    def json_stream(self, on: bool = True):
+        """The following ingest_json calls are the batches of one stream: rows numbered by arrival across batches, ids of
+        namespaces and codes of phase strings persistent (pte_json_stream)."""
+        self._ck(self._L.pte_json_stream(self._h, 1 if on else 0))
+
     def json_timing(self) -> Dict[str, float]:
         """Device time of the last ingest_json: {"ms_index", "ms_parse", "text_bytes"} (pte_json_timing)."""
         a, b, n = C.c_float(), C.c_float(), C.c_uint64()

@@ -48,6 +48,26 @@ from .engine import EmittedColumns, PhaseTransitionEngine, PteError
 from .replay_log import ReplayLog
 
 
+class _RawJsonLog:
+    """What Batch needs of a log, for a chunk of raw watch lines: the pod object of line i, made on demand."""
+
+    def __init__(self, text: bytes, n: int, deserialize):
+        self._lines = text.split(b"\n")
+        self._n, self._deserialize = n, deserialize
+        self._pods = {}              # (not None: bodies are built from the objects, not on the device)
+        self.deserialized = 0
+
+    def __len__(self):
+        return self._n
+
+    def pod_at(self, i: int):
+        pod = self._pods.get(i)
+        if pod is None:
+            pod = self._pods[i] = self._deserialize(self._lines[i])
+            self.deserialized += 1
+        return pod
+
+
 class Batch:
     """Emitted notifications of one replay, in replay order."""
 
@@ -382,6 +402,46 @@ class PodWatcher:
         batch = Batch(self, log, eng.fetch(columns=("idx", "type")), stats, dedupe)
         self._remember(batch)
         return batch
+
+    def watch_json(self, chunks, deserialize, *, dedupe: Optional[bool] = None) -> List[Batch]:
+        """The live loop over the RAW watch stream (what the API server sends for ``?watch=true``, before any client has
+        turned it into objects): ``chunks`` yields bytes, each a run of whole lines, one JSON watch event per line, in
+        arrival order.  Every chunk is parsed, filtered and compared with the stream's per-pod state on the device
+        (pte_json_stream + PTE_RUN_CARRY); ``deserialize(line) -> pod object`` is called ONLY for the lines that lead to
+        a notification -- with the kubernetes client that is the expensive step of ``for event in w.stream(...)``
+        (pod_watcher.py:264-269), and under the production filter most events never need it.  Payloads and sink calls are
+        those of the object loop.  Returns the batches."""
+        dedupe = self.dedupe if dedupe is None else dedupe
+        names = self.config.get("watcher", {}).get("namespaces", []) or []
+        out: List[Batch] = []
+        started = False
+        for chunk in chunks:
+            if not chunk.strip():
+                continue
+            n_lines = chunk.count(b"\n") + (0 if chunk.endswith(b"\n") else 1)
+            if self._engine is None:
+                self._engine = PhaseTransitionEngine(max(self.flush_every or 0, n_lines, 1024), self.max_pods, device=self._device)
+            elif self._engine.max_events < n_lines:
+                self._engine.grow(n_lines)
+            eng = self._engine
+            if not started:
+                eng.json_stream(True)
+                started = True
+            n = eng.ingest_json(chunk)
+            known = eng.json_strings(0)                    # the stream's namespaces so far, index = ns_id
+            eng.set_filters([i for i, nm in enumerate(known) if nm in names], ns_filter_on=bool(names),
+                            critical_only=self._critical_only())
+            stats = eng.run(dedupe=dedupe, carry=True)
+            batch = Batch(self, _RawJsonLog(chunk, n, deserialize), eng.fetch(columns=("idx", "type")), stats, dedupe)
+            self._remember(batch)
+            out.append(batch)
+            if self.clusterapi_client is not None:
+                sent = self.clusterapi_client.update_pod_status_batch(batch)
+                if sent != len(batch):
+                    self.logger.error("Failed to notify clusterapi about %d of %d events", len(batch) - sent, len(batch))
+        if started:
+            self._engine.json_stream(False)
+        return out
 
     def _stream_mode(self) -> bool:
         return bool(self.flush_every) or self.flush_interval is not None

@@ -422,3 +422,54 @@ def test_device_json_decodes_escapes_in_every_field_it_reads():
         assert np.array_equal(got.columns[k], want.columns[k]), k
     assert got.namespaces == want.namespaces and np.array_equal(got.columns["ns_id"], want.columns["ns_id"])
     assert got.phases == want.phases and np.array_equal(got.columns["phase"], want.columns["phase"])
+
+
+# ---- the raw watch stream as a live loop (SURVEY 8f rows 1 + 2): chunks of lines, state carried on the device ---------
+@pytest.mark.gpu
+@pytest.mark.parametrize("env", ["development", "staging", "production"])
+def test_raw_watch_stream_in_chunks_notifies_like_the_object_loop(env, monkeypatch):
+    """PodWatcher.watch_json: the same notifications as the reference's filters + transition layer over the whole
+    stream, however the stream is cut into chunks; pod objects are made only for lines that lead to a notification."""
+    from k8s_watcher_b200 import ClusterApiClient
+    from mock_transport import MockTransport
+    monkeypatch.chdir(ROOT)
+    n, pods = 30_000, 250
+    cols = c_oracle.generate(SEED + 21, n, pods, dist=1, p_del=0.1, p_nostatus=0.05, p_null=0.05)
+    events = fk.events_from_columns(cols)
+    odd = ("Terminating", "Evicted", "ContainerCreating", "Weird\\Phase")
+    for k in range(0, n, 61):
+        if events[k]["object"].status is not None:
+            events[k]["object"].status.phase = odd[(k // 61 * 7 + k) % len(odd)]     # custom phases, first seen in different chunks
+    for k in range(0, n, 97):
+        events[k]["object"].metadata.namespace = ("late-namespace-%d" % (k % 5), "production")[k % 2]
+    lines = [l for l in fk.watch_json_lines(events, seed=8).split(b"\n") if l]
+    assert len(lines) == n
+    where = {l: i for i, l in enumerate(lines)}
+    assert len(where) == n
+    rnd = np.random.default_rng(3)
+    cuts = [0]
+    while cuts[-1] < n:
+        cuts.append(min(n, cuts[-1] + int(rnd.choice([1, 5, 300, 2500, 4096, 4097, 7000]))))
+    chunks = [b"\n".join(lines[a:b]) + (b"\n" if k % 2 else b"") for k, (a, b) in enumerate(zip(cuts[:-1], cuts[1:]))]
+    calls = []
+
+    def deserialize(line):
+        calls.append(where[line])
+        return events[where[line]]["object"]
+
+    sink = ClusterApiClient("http://clusterapi.invalid", transport=MockTransport())
+    w = PodWatcher(env, sink=sink, max_pods=1024, keep_batches=None)
+    batches = w.watch_json(iter(chunks), deserialize)
+    got = np.concatenate([b.indices.astype(np.int64) + a for b, a in zip(batches, cuts[:-1])])
+    r = po.reference_trace(env, w.config, [(e["type"], e["object"]) for e in events], "T")
+    keep = po.transition_filter(r)
+    reach = [i for i, e in enumerate(events) if po.reaches_post_site(env, w.config, e["type"], e["object"])]
+    want = [reach[k] for k in keep]
+    assert got.tolist() == want
+    assert sorted(calls) == want                                   # objects only for what is notified
+    bodies = [json.loads(b) for b in sink.transport.bodies()]
+    assert [b["uid"] for b in bodies] == [events[i]["object"].metadata.uid for i in want]
+    assert [b["event_type"] for b in bodies] == [events[i]["type"] for i in want]
+    # the stream mode ends with the loop: a one-shot replay of the whole text afterwards is its own log again
+    one = w.replay_watch_json(b"\n".join(lines))
+    assert one.indices.tolist() == want
