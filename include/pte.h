@@ -136,19 +136,22 @@ int pte_ingest(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, con
  * API streams them and the reference's loop receives them (event['type'], event['object'], pod_watcher.py:264-268):
  *   {"type":"MODIFIED","object":{"metadata":{"uid":..,"namespace":..,"resourceVersion":..},"status":{"phase":..},..}}
  * Keys in any order, any whitespace; the rest of the object is skipped (nesting- and string-aware).  Replaces
- * the current log.  uid must be a 128-bit hex uid (dashes ignored); a missing resourceVersion becomes line
- * number + 1; status absent or null -> PTE_PH_NOSTATUS, phase absent or null -> PTE_PH_NULL.  Namespaces, and phase
+ * the current log.  metadata.uid in the form Kubernetes emits (lower-case hex, 8-4-4-4-12) is its own 128-bit key; any other
+ * uid string -- the reference takes whatever arrives, pod_watcher.py:164 -- is interned exactly on the device and gets the key
+ * (2^64 - 1, k), k = 1, 2, ... in order of first occurrence (pte_json_strings(which = 2) returns those strings, index k - 1;
+ * canonical strings whose value lies in that block, and the all-zero uid, go the same way): two different uid strings never
+ * share a key.  A missing resourceVersion becomes line number + 1; status absent or null -> PTE_PH_NOSTATUS, phase absent or null -> PTE_PH_NULL.  Namespaces, and phase
  * strings other than the five well-known ones, are interned exactly on the device (ids / codes >= 7 in order of
  * first occurrence); pte_json_strings returns the dictionaries.  JSON escape sequences in the five strings are decoded
  * (\" \\ \/ \b \f \n \r \t, \uXXXX with surrogate pairs, as UTF-8): two spellings of one string are one string, and
- * pte_json_strings returns the decoded bytes.  On a bad line (not one JSON container, type / uid / resourceVersion not
- * of the form above, a broken escape): PTE_ERR_PARSE, *bad_line = its 0-based number, and the log is left empty. */
+ * pte_json_strings returns the decoded bytes.  On a bad line (not one JSON container, type / resourceVersion not
+ * of the form above, no uid string, a broken escape): PTE_ERR_PARSE, *bad_line = its 0-based number, and the log is left empty. */
 int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_events, uint64_t* bad_line);
 
 /* Raw watch text as a STREAM (the body of `for event in w.stream(...)`, pod_watcher.py:264-269, fed from the wire in pieces):
  * with on != 0 every following pte_ingest_json is the next batch of one stream -- rows are numbered by arrival across the
  * batches (that number is the order key; metadata.resourceVersion is not read, as in the reference's loop), and a
- * namespace or phase string keeps the id / code it got when the stream first showed it, so PTE_RUN_CARRY compares like with
+ * namespace, phase or non-UUID uid string keeps the id / code / key it got when the stream first showed it, so PTE_RUN_CARRY compares like with
  * like and pte_json_strings returns the stream's dictionaries so far.  Each call (on or off) starts afresh. */
 int pte_json_stream(pte_handle h, int on);
 
@@ -156,7 +159,8 @@ int pte_json_stream(pte_handle h, int on);
  * the line index (count, scan, list of newlines) and the scanner kernel; text_bytes = size of that log. */
 int pte_json_timing(pte_handle h, float* ms_index, float* ms_parse, uint64_t* text_bytes);
 
-/* Dictionary of the last pte_ingest_json: which = 0 namespaces (index = ns_id), 1 phase strings (index = code - 7).
+/* Dictionary of the last pte_ingest_json: which = 0 namespaces (index = ns_id), 1 phase strings (index = code - 7),
+ * 2 uid strings that are not canonical UUIDs (index = uid_lo - 1 of the rows with uid_hi == 2^64 - 1).
  * Strings are written back to back into buf, offsets[0..n] delimit them; buf == NULL just counts (*n_out). */
 int pte_json_strings(pte_handle h, int which, char* buf, uint64_t cap, uint32_t* offsets, uint32_t max_entries,
                      uint32_t* n_out);

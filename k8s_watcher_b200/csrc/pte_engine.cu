@@ -129,10 +129,11 @@ struct pte_engine {
     u32* json_chunk_cnt = nullptr; u64 json_chunk_cap = 0;
     u64* json_ns_keys = nullptr; u32* json_ns_off = nullptr; u64* json_ph_keys = nullptr; u32* json_ph_off = nullptr;
     u32 *json_err = nullptr, *json_ns_remap = nullptr; u8* json_ph_remap = nullptr;
-    std::vector<std::string> json_names[2];                  // [0] namespaces by ns_id, [1] phase strings for codes >= 7
+    std::vector<std::string> json_names[3];                  // [0] namespaces by ns_id, [1] phase strings for codes >= 7, [2] non-UUID uid strings by reserved key - 1
+    u64* json_uid_keys = nullptr; u32 *json_uid_off = nullptr, *json_uid_remap = nullptr; bool json_uid_dirty = true;
     // pte_json_stream: the logs ingested are the batches of ONE stream -- ids and codes of names persist, rows are numbered by arrival
     bool json_stream = false; u64 json_seq = 0;
-    std::unordered_map<std::string, u32> json_ids[2];
+    std::unordered_map<std::string, u32> json_ids[3];
     u64* d_minmax = nullptr;
     float ms_payload = 0.f; u64 payload_bytes = 0;            // device time of the last payload_write_kernel
     float ms_json[2] = {0.f, 0.f}; u64 json_bytes = 0;        // device times of the last pte_ingest_json
@@ -544,7 +545,8 @@ void pte_destroy(pte_handle h) {
                     h->out_type, h->d_counts_send, h->d_counts_recv, h->shadow.uid_hi, h->shadow.uid_lo, h->shadow.rv,
                     h->shadow.ns, h->shadow.phase, h->shadow.type, h->perm, h->d_minmax, h->pay_buf, h->pay_blob,
                     h->pay_frag_off, h->pay_rec_off, h->pay_tile_off, h->json_text, h->json_nl, h->json_chunk_cnt, h->json_ns_keys, h->json_ns_off,
-                    h->json_ph_keys, h->json_ph_off, h->json_err, h->json_ns_remap, h->json_ph_remap, h->tiny_in_dev, h->tiny_out_dev};
+                    h->json_ph_keys, h->json_ph_off, h->json_err, h->json_ns_remap, h->json_ph_remap, h->json_uid_keys, h->json_uid_off, h->json_uid_remap,
+                    h->tiny_in_dev, h->tiny_out_dev};
     for (void* b : bufs) if (b) cudaFree(b);
     if (h->tiny_in_host) cudaFreeHost(h->tiny_in_host);
     if (h->tiny_out_host) cudaFreeHost(h->tiny_out_host);
@@ -1342,7 +1344,7 @@ int pte_serialize_payloads(pte_handle h, uint64_t first, uint64_t count, const c
     return PTE_OK;
 }
 
-static constexpr u32 kJsonNsSlots = 1u << 16, kJsonPhSlots = 128;
+static constexpr u32 kJsonNsSlots = 1u << 16, kJsonPhSlots = 128, kJsonUidSlots = 1u << 20;      // uid strings that are not canonical UUIDs
 
 struct HostJsonText { const char* base; __host__ __device__ char operator[](u32 i) const { return base[i]; } };
 
@@ -1354,7 +1356,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
     h->has_run = false;
-    if (!h->json_stream) { h->json_names[0].clear(); h->json_names[1].clear(); }
+    if (!h->json_stream) { for (auto& v : h->json_names) v.clear(); }
     if (len == 0) { h->n_events = 0; return PTE_OK; }
     int rc;
     if ((rc = grow(h, &h->json_text, &h->json_text_cap, len + 64))) return rc;
@@ -1387,6 +1389,15 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
         CK(h, cudaMalloc((void**)&h->json_err, 4 * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_ns_remap, kJsonNsSlots * sizeof(u32)));
         CK(h, cudaMalloc((void**)&h->json_ph_remap, kJsonPhSlots));
+        CK(h, cudaMalloc((void**)&h->json_uid_keys, kJsonUidSlots * sizeof(u64)));
+        CK(h, cudaMalloc((void**)&h->json_uid_off, kJsonUidSlots * sizeof(u32)));
+        CK(h, cudaMalloc((void**)&h->json_uid_remap, kJsonUidSlots * sizeof(u32)));
+        h->json_uid_dirty = true;
+    }
+    if (h->json_uid_dirty) {                                       // (12 MB: only after a log that had such uids)
+        CK(h, cudaMemsetAsync(h->json_uid_keys, 0, kJsonUidSlots * sizeof(u64), st));
+        CK(h, cudaMemsetAsync(h->json_uid_off, 0xFF, kJsonUidSlots * sizeof(u32), st));
+        h->json_uid_dirty = false;
     }
     CK(h, cudaMemsetAsync(h->json_ns_keys, 0, kJsonNsSlots * sizeof(u64), st));
     CK(h, cudaMemsetAsync(h->json_ns_off, 0xFF, kJsonNsSlots * sizeof(u32), st));
@@ -1399,6 +1410,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     a.uid_hi = h->uid_hi; a.uid_lo = h->uid_lo; a.rv = h->rv; a.ns = h->ns; a.phase = h->phase; a.type = h->type;
     a.ns_dict = StrDict{h->json_ns_keys, h->json_ns_off, kJsonNsSlots - 1};
     a.phase_dict = StrDict{h->json_ph_keys, h->json_ph_off, kJsonPhSlots - 1};
+    a.uid_dict = StrDict{h->json_uid_keys, h->json_uid_off, kJsonUidSlots - 1};
     a.err = h->json_err;
     a.arrival_order = h->json_stream ? 1 : 0; a.arrival_base = h->json_seq;
     grid = (int)std::min<u64>((n_lines + kJsonThreads - 1) / kJsonThreads, (u64)h->num_sms * 8);
@@ -1406,7 +1418,7 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     json_parse_kernel<<<grid, kJsonThreads, 0, st>>>(a, h->json_err + 2);
     CK(h, cudaGetLastError());
     CK(h, cudaEventRecord(h->ev[2], st));
-    u32 err[2];
+    u32 err[4];                                                   // [3]: rows whose uid went through the uid dictionary
     CK(h, cudaMemcpyAsync(err, h->json_err, sizeof(err), cudaMemcpyDeviceToHost, st));
     std::vector<u64> nk(kJsonNsSlots), pk(kJsonPhSlots);
     std::vector<u32> no(kJsonNsSlots), po(kJsonPhSlots);
@@ -1415,10 +1427,11 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     CK(h, cudaMemcpyAsync(pk.data(), h->json_ph_keys, pk.size() * 8, cudaMemcpyDeviceToHost, st));
     CK(h, cudaMemcpyAsync(po.data(), h->json_ph_off, po.size() * 4, cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
+    if (err[3]) h->json_uid_dirty = true;
     if (err[0]) {
-        static const char* why[] = {"", "malformed JSON", "event type is not ADDED/MODIFIED/DELETED", "metadata.uid is not a 128-bit hex uid",
+        static const char* why[] = {"", "malformed JSON", "event type is not ADDED/MODIFIED/DELETED", "metadata.uid is missing or not a string",
                                     "metadata.resourceVersion is not a decimal number", "a field the path reads contains a broken escape sequence",
-                                    "more distinct namespaces than the device dictionary holds", "too many distinct phase strings"};
+                                    "more distinct strings than a device dictionary holds (65 536 namespaces, 1 048 576 uids that are not canonical UUIDs per log)", "too many distinct phase strings"};
         if (bad_line) *bad_line = err[1];
         h->n_events = 0;
         FAIL(h, PTE_ERR_PARSE, std::string("watch log line ") + std::to_string(err[1]) + ": " + why[std::min<u32>(err[0], 7)]);
@@ -1454,8 +1467,21 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
     for (u32 sl = 0; sl < kJsonPhSlots; sl++) premap[sl] = (u8)(7 + premap32[sl]);
     CK(h, cudaMemcpyAsync(h->json_ns_remap, nremap.data(), nremap.size() * 4, cudaMemcpyHostToDevice, st));
     CK(h, cudaMemcpyAsync(h->json_ph_remap, premap.data(), premap.size(), cudaMemcpyHostToDevice, st));
+    const u32* uid_remap = nullptr;
+    if (err[3]) {
+        // some uids are not canonical UUIDs: their dictionary slots -> keys of the reserved block (1, 2, ... in order of first
+        // occurrence; in a stream a string keeps the key it got first)
+        std::vector<u64> uk(kJsonUidSlots);
+        std::vector<u32> uo(kJsonUidSlots), uremap;
+        CK(h, cudaMemcpyAsync(uk.data(), h->json_uid_keys, uk.size() * 8, cudaMemcpyDeviceToHost, st));
+        CK(h, cudaMemcpyAsync(uo.data(), h->json_uid_off, uo.size() * 4, cudaMemcpyDeviceToHost, st));
+        CK(h, cudaStreamSynchronize(st));
+        build(uk, uo, h->json_names[2], uremap, h->json_ids[2]);
+        CK(h, cudaMemcpyAsync(h->json_uid_remap, uremap.data(), uremap.size() * 4, cudaMemcpyHostToDevice, st));
+        uid_remap = h->json_uid_remap;
+    }
     grid = (int)std::min<u64>((n_lines + 255) / 256, (u64)h->num_sms * 16);
-    json_remap_kernel<<<grid, 256, 0, st>>>(h->ns, h->phase, n_lines, h->json_ns_remap, h->json_ph_remap);
+    json_remap_kernel<<<grid, 256, 0, st>>>(h->ns, h->phase, n_lines, h->json_ns_remap, h->json_ph_remap, h->uid_hi, h->uid_lo, uid_remap);
     CK(h, cudaGetLastError());
     u64 ends[2] = {0, 0};
     CK(h, cudaMemcpyAsync(&ends[0], h->rv, sizeof(u64), cudaMemcpyDeviceToHost, st));
@@ -1475,7 +1501,7 @@ int pte_json_stream(pte_handle h, int on) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     h->json_stream = on != 0;
     h->json_seq = 0;
-    for (int k = 0; k < 2; k++) { h->json_names[k].clear(); h->json_ids[k].clear(); }
+    for (int k = 0; k < 3; k++) { h->json_names[k].clear(); h->json_ids[k].clear(); }
     return PTE_OK;
 }
 
@@ -1495,7 +1521,7 @@ int pte_json_timing(pte_handle h, float* ms_index, float* ms_parse, uint64_t* te
 }
 
 int pte_json_strings(pte_handle h, int which, char* buf, uint64_t cap, uint32_t* offsets, uint32_t max_entries, uint32_t* n_out) {
-    if (!h || !n_out || which < 0 || which > 1) FAIL(h, PTE_ERR_INVALID, "bad argument");
+    if (!h || !n_out || which < 0 || which > 2) FAIL(h, PTE_ERR_INVALID, "bad argument");
     const auto& v = h->json_names[which];
     *n_out = (u32)v.size();
     if (!buf || !offsets) return PTE_OK;

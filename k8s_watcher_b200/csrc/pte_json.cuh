@@ -151,7 +151,7 @@ struct JsonArgs {
     const u64* nl; u64 n_lines;            // line i = [i ? nl[i-1] + 1 : 0, i < n_nl ? nl[i] : len)
     u64 n_nl;
     u64* uid_hi; u64* uid_lo; u64* rv; u32* ns; u8* phase; u8* type;
-    StrDict ns_dict, phase_dict;
+    StrDict ns_dict, phase_dict, uid_dict;
     u32* err;          // [0] worst error code, [1] (via atomicMin) first bad line + 1
     int arrival_order; u64 arrival_base;   // stream mode: row i gets the order key arrival_base + i + 1, resourceVersion is not read
 };
@@ -171,20 +171,24 @@ __device__ __forceinline__ bool parse_type(const A& t, u32 s, u32 len, u32& type
     for (u32 k = 1; k < len; k++) ok = ok && t[s + k] == name[k];
     return ok;
 }
+// metadata.uid (:164) in the form Kubernetes emits -- lower-case hex, 8-4-4-4-12 -- is its own 128-bit key.  Whatever else
+// arrives (the reference takes any string) is interned exactly in a string dictionary and gets a key of the reserved block
+// hi == kUidReservedHi; so do the canonical strings whose value lies in that block or is zero.  Two different uid strings
+// never share a key.  (codes.UidInterner is the host's form of the same rule.)
+static constexpr u64 kUidReservedHi = 0xFFFFFFFFFFFFFFFFull;
 template <typename A>
-__device__ __forceinline__ bool parse_uid(const A& t, u32 s, u32 len, u64& hi, u64& lo) {
-    // metadata.uid (:164): 32 hex digits, dashes ignored
-    u32 nd = 0;
+__device__ __forceinline__ bool parse_canonical_uid(const A& t, u32 s, u32 len, u64& hi, u64& lo) {
+    if (len != 36) return false;
     hi = lo = 0;
-    for (u32 k = 0; k < len; k++) {
+    for (u32 k = 0; k < 36; k++) {
         const char c = t[s + k];
-        if (c == '-') continue;
-        const int v = ptejson::hex_digit(c);
-        if (v < 0 || nd >= 32) return false;
+        if (k == 8 || k == 13 || k == 18 || k == 23) { if (c != '-') return false; continue; }
+        int v;
+        if (c >= '0' && c <= '9') v = c - '0'; else if (c >= 'a' && c <= 'f') v = c - 'a' + 10; else return false;
+        const u32 nd = k - (k > 8) - (k > 13) - (k > 18) - (k > 23);
         if (nd < 16) hi = (hi << 4) | (u64)v; else lo = (lo << 4) | (u64)v;
-        nd++;
     }
-    return nd == 32 && (hi | lo) != 0;
+    return hi != kUidReservedHi && (hi | lo) != 0;
 }
 template <typename A>
 __device__ __forceinline__ bool parse_rv(const A& t, u32 s, u32 len, u64& rv) {
@@ -255,13 +259,20 @@ __device__ __forceinline__ void json_line(const JsonArgs& a, const T& t, u64 i, 
     }
     if (!bad) {
         const u32 s = span_start(f.uid), len = span_len(f.uid);
-        bool ok = span_present(f.uid);
-        if (ok && has_backslash(t, s, len)) {
-            const u32 r = decode_small(t, s, len, buf, n);
-            if (r == 2) bad = kJsonEscapedField;
-            ok = r == 0 && parse_uid(LocalText{buf}, 0, n, hi, lo);
-        } else ok = ok && parse_uid(t, s, len, hi, lo);
-        if (!bad && !ok) bad = kJsonBadUid;
+        if (!span_present(f.uid)) bad = kJsonBadUid;               // no uid string at all
+        else {
+            bool direct;
+            if (has_backslash(t, s, len)) {
+                const u32 r = decode_small(t, s, len, buf, n);
+                if (r == 2) bad = kJsonEscapedField;
+                direct = r == 0 && parse_canonical_uid(LocalText{buf}, 0, n, hi, lo);
+            } else direct = parse_canonical_uid(t, s, len, hi, lo);
+            if (!bad && !direct) {
+                hi = kUidReservedHi;
+                lo = dict_intern(a.uid_dict, t, s, len, bad);      // slot for now; json_remap_kernel turns it into the key
+                atomicAdd(a.err + 3, 1u);
+            }
+        }
     }
     if (a.arrival_order) rv = a.arrival_base + i + 1;      // the reference's loop knows no other order (it never reads resourceVersion)
     else if (!bad && span_present(f.rv)) {
@@ -319,9 +330,11 @@ __global__ void __launch_bounds__(kJsonThreads, PTE_JSON_BLOCKS) json_parse_kern
 
 // dictionary slots -> dense ids in order of first occurrence (remap tables built by the host)
 __global__ void __launch_bounds__(256)
-json_remap_kernel(u32* __restrict__ ns, u8* __restrict__ phase, u64 n, const u32* __restrict__ ns_remap, const u8* __restrict__ phase_remap) {
+json_remap_kernel(u32* __restrict__ ns, u8* __restrict__ phase, u64 n, const u32* __restrict__ ns_remap, const u8* __restrict__ phase_remap,
+                  const u64* __restrict__ uid_hi, u64* __restrict__ uid_lo, const u32* __restrict__ uid_remap) {
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
         ns[i] = ns_remap[ns[i]];
+        if (uid_remap && uid_hi[i] == kUidReservedHi) uid_lo[i] = (u64)uid_remap[uid_lo[i]] + 1;      // reserved keys start at 1
         const u8 ph = phase[i];
         if (ph & 0x80u) phase[i] = phase_remap[ph & 0x7Fu];
     }

@@ -188,7 +188,8 @@ class PhaseTransitionEngine:
         return {"ms_index": a.value, "ms_parse": b.value, "text_bytes": int(n.value)}
 
     def json_strings(self, which: int) -> list:
-        """Dictionary of the last ingest_json: 0 = namespaces by ns_id, 1 = phase strings for codes 7, 8, ..."""
+        """Dictionary of the last ingest_json: 0 = namespaces by ns_id, 1 = phase strings for codes 7, 8, ...,
+        2 = uid strings that are not canonical UUIDs (index = uid_lo - 1 where uid_hi == 2**64 - 1)."""
         n = C.c_uint32()
         self._ck(self._L.pte_json_strings(self._h, which, None, 0, None, 0, C.byref(n)))
         if n.value == 0:

@@ -122,7 +122,14 @@ class ReplayLog:
         (pte_ingest_json).  The log is left resident in ``engine``, ready for ``engine.run()``."""
         engine.ingest_json(text)
         phases = list(codes.PHASE_NAMES) + [None, None] + engine.json_strings(1)
-        return cls(engine.read_log(), engine.json_strings(0), phases)
+        log = cls(engine.read_log(), engine.json_strings(0), phases)
+        odd = engine.json_strings(2)
+        if odd:                       # uid strings that are not canonical UUIDs: the device's keys for them, and the way back
+            log.uids = codes.UidInterner()
+            for name in odd:
+                log.uids._ids[name] = len(log.uids._strings) + 1
+                log.uids._strings.append(name)
+        return log
 
     @classmethod
     def synthetic(cls, seed: int, n_events: int, n_pods: int, **kw) -> "ReplayLog":

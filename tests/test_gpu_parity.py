@@ -552,7 +552,8 @@ def test_replay_of_watch_json_matches_reference_semantics(env, monkeypatch):
 
 
 @pytest.mark.parametrize("bad,reason", [
-    (b'{"type":"ADDED","object":{"metadata":{"uid":"zz","namespace":"a"}}}', "uid"),
+    (b'{"type":"ADDED","object":{"metadata":{"uid":5,"namespace":"a"}}}', "uid"),
+    (b'{"type":"ADDED","object":{"metadata":{"namespace":"a"}}}', "uid"),
     (b'{"type":"BOOKMARK","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001"}}}', "type"),
     (b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001","resourceVersion":"12x"}}}', "resourceVersion"),
     (b'{"type":"ADDED","object":{"metadata":{"uid":"00000000-0000-0000-0000-000000000001"}', "malformed"),

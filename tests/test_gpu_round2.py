@@ -473,3 +473,51 @@ def test_raw_watch_stream_in_chunks_notifies_like_the_object_loop(env, monkeypat
     # the stream mode ends with the loop: a one-shot replay of the whole text afterwards is its own log again
     one = w.replay_watch_json(b"\n".join(lines))
     assert one.indices.tolist() == want
+
+
+@pytest.mark.gpu
+def test_device_json_keeps_uid_strings_of_any_form_apart(monkeypatch):
+    """metadata.uid is whatever string arrives (pod_watcher.py:164): canonical UUIDs are their own key, every other string
+    gets a key of the reserved block -- one string one key, also across the chunks of a stream, and the replay equals the
+    object loop's."""
+    monkeypatch.chdir(ROOT)
+    n, pods = 12_000, 300
+    cols = c_oracle.generate(SEED + 31, n, pods, dist=1, p_del=0.1, p_nostatus=0.03, p_null=0.03)
+    events = fk.events_from_columns(cols)
+    canon = {}
+    for ev in events:                      # every third pod gets a uid that is no canonical UUID, in several flavours
+        md = ev["object"].metadata
+        p = int(md.name.split("-")[1])
+        if p % 3 == 0:
+            flavours = ("pod-uid-%d", "%032x", "ABCDEF00-0000-4000-8000-%012X", "ffffffff-ffff-ffff-0000-%012x", "wei\\rd \"uid\" é %d")
+            canon.setdefault(md.uid, flavours[p // 3 % len(flavours)] % p)
+            md.uid = canon[md.uid]
+    events[7]["object"].metadata.uid = ""                                     # even the empty string is a uid string
+    events[9]["object"].metadata.uid = "00000000-0000-0000-0000-000000000000"   # the all-zero uid cannot be its own key
+    text = fk.watch_json_lines(events, seed=12)
+    lines = [l for l in text.split(b"\n") if l]
+    with PhaseTransitionEngine(n, pods + 10) as e:
+        log = ReplayLog.from_watch_json(e, text)
+    keys = list(zip(log.columns["uid_hi"].tolist(), log.columns["uid_lo"].tolist()))
+    strings = [ev["object"].metadata.uid for ev in events]
+    by_key, by_string = {}, {}
+    for k, s_ in zip(keys, strings):
+        assert by_key.setdefault(k, s_) == s_ and by_string.setdefault(s_, k) == k          # a bijection
+    reserved = [(k, s_) for k, s_ in by_key.items() if k[0] == 0xFFFFFFFFFFFFFFFF]
+    assert len(reserved) == len({s_ for s_ in strings if by_string[s_][0] == 0xFFFFFFFFFFFFFFFF}) > 90
+    for k, s_ in by_key.items():
+        assert log.uids.string(*k) == s_ if k[0] == 0xFFFFFFFFFFFFFFFF else codes_uid(k) == s_
+    # and the whole thing as a stream in chunks: same notifications as the object loop with the same odd uids
+    where = {l: i for i, l in enumerate(lines)}
+    w = PodWatcher("staging", max_pods=1024, keep_batches=None)
+    cuts = list(range(0, n, 1700)) + [n]
+    chunks = [b"\n".join(lines[a:b]) for a, b in zip(cuts[:-1], cuts[1:])]
+    batches = w.watch_json(iter(chunks), lambda line: events[where[line]]["object"])
+    got = np.concatenate([b.indices.astype(np.int64) + a for b, a in zip(batches, cuts[:-1])])
+    r = po.reference_trace("staging", w.config, [(ev["type"], ev["object"]) for ev in events], "T")
+    assert got.tolist() == po.transition_filter(r)
+
+
+def codes_uid(k):
+    from k8s_watcher_b200 import codes
+    return codes.uid_to_str(*k)
