@@ -152,7 +152,8 @@ int pte_ingest_json(pte_handle h, const char* text, uint64_t len, uint64_t* n_ev
  * with on != 0 every following pte_ingest_json is the next batch of one stream -- rows are numbered by arrival across the
  * batches (that number is the order key; metadata.resourceVersion is not read, as in the reference's loop), and a
  * namespace, phase or non-UUID uid string keeps the id / code / key it got when the stream first showed it, so PTE_RUN_CARRY compares like with
- * like and pte_json_strings returns the stream's dictionaries so far.  Each call (on or off) starts afresh. */
+ * like and pte_json_strings returns the stream's dictionaries so far.  Each call (on or off) starts afresh: names, numbering,
+ * and the per-pod state carried by earlier PTE_RUN_CARRY runs. */
 int pte_json_stream(pte_handle h, int on);
 
 /* Device time of the last pte_ingest_json (CUDA events on the engine stream, host <-> device copies excluded):

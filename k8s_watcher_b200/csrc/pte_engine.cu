@@ -1501,6 +1501,7 @@ int pte_json_stream(pte_handle h, int on) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     h->json_stream = on != 0;
     h->json_seq = 0;
+    h->carry_valid = false;          // a stream carried so far (PTE_RUN_CARRY) ends here: its order keys mean nothing to the next one
     for (int k = 0; k < 3; k++) { h->json_names[k].clear(); h->json_ids[k].clear(); }
     return PTE_OK;
 }

@@ -414,6 +414,13 @@ class PodWatcher:
         dedupe = self.dedupe if dedupe is None else dedupe
         names = self.config.get("watcher", {}).get("namespaces", []) or []
         out: List[Batch] = []
+        try:
+            return self._watch_json(chunks, deserialize, dedupe, names, out)
+        finally:
+            if self._engine is not None:
+                self._engine.json_stream(False)          # whatever ended the loop, the next log is its own log again
+
+    def _watch_json(self, chunks, deserialize, dedupe, names, out) -> List[Batch]:
         started = False
         for chunk in chunks:
             if not chunk.strip():
@@ -439,8 +446,6 @@ class PodWatcher:
                 sent = self.clusterapi_client.update_pod_status_batch(batch)
                 if sent != len(batch):
                     self.logger.error("Failed to notify clusterapi about %d of %d events", len(batch) - sent, len(batch))
-        if started:
-            self._engine.json_stream(False)
         return out
 
     def _stream_mode(self) -> bool:

@@ -521,3 +521,28 @@ def test_device_json_keeps_uid_strings_of_any_form_apart(monkeypatch):
 def codes_uid(k):
     from k8s_watcher_b200 import codes
     return codes.uid_to_str(*k)
+
+
+@pytest.mark.gpu
+def test_raw_watch_loop_after_an_object_loop_on_the_same_watcher(monkeypatch):
+    """watch_json starts its own stream even if the watcher's engine carried another one before, and leaves the engine
+    ready for one-shot logs when it ends -- also when it ends with an error."""
+    monkeypatch.chdir(ROOT)
+    n, pods = 5000, 60
+    cols = c_oracle.generate(SEED + 41, n, pods, dist=0, p_del=0.1)
+    events = fk.events_from_columns(cols)
+    lines = [l for l in fk.watch_json_lines(events, seed=1).split(b"\n") if l]
+    where = {l: i for i, l in enumerate(lines)}
+    r = po.transition_filter(po.reference_trace("staging", PodWatcher("staging").config, [(e["type"], e["object"]) for e in events], "T"))
+    w = PodWatcher("staging", flush_every=1000, flush_interval=None, max_pods=256, keep_batches=None)
+    for ev in events[:2500]:                                   # an object loop first: its stream is at arrival number 2500
+        w.handle_pod_event(ev["type"], ev["object"])
+    w.flush()
+    chunks = [b"\n".join(lines[a:a + 900]) for a in range(0, n, 900)]
+    batches = w.watch_json(iter(chunks), lambda line: events[where[line]]["object"])
+    got = np.concatenate([b.indices.astype(np.int64) + 900 * k for k, b in enumerate(batches)])
+    assert got.tolist() == r
+    with pytest.raises(PteError):                              # a broken line ends the loop ...
+        w.watch_json(iter([chunks[0], b'{"type":"ADDED"', chunks[1]]), lambda line: events[where[line]]["object"])
+    one = w.replay_watch_json(b"\n".join(lines))               # ... and the engine takes one-shot logs as before
+    assert one.indices.tolist() == r
