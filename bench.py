@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-packed-meta", action="store_true",
+                    help="the e2e log carries type << 6 | phase as ONE byte per event (ReplayLog.pack_meta, done while the log is built: untimed): 17 instead of 18 B/event over PCIe")
     ap.add_argument("--total-events", type=float, default=None,
                     help="BASELINE config 5 literally: this many events in total over the N GPUs (e.g. 8e9)")
     return ap.parse_args()
@@ -502,6 +504,8 @@ def _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m, shard=Non
     log = ReplayLog.pinned(m, list(codes.DEFAULT_NAMESPACES))
     eng.read_log(into=log.columns)                                            # set-up, untimed
     log.arrival_ordered = True            # the synthetic log is generated in replay order: the rv column stays on the host
+    if args.e2e_packed_meta:
+        log.pack_meta()
     w = PodWatcher("staging", engine=eng, config_dir=os.path.join(ROOT, "config"), keep_batches=1)
     w.logger.disabled = True
     batch = w.replay(log)                                                     # warm-up
@@ -517,11 +521,11 @@ def _e2e(eng, args, np, PinnedBuffer, ev, barrier, wl, rank, world, m, shard=Non
     h2d_s = time.perf_counter() - t1
     barrier()
     res = {"value": None, "unit": UNIT, "ms_per_step": ms, "steps": args.e2e_steps, "events_per_gpu": m,
-           "h2d_bytes_per_step": 18 * m, "d2h_bytes_per_step": 4 * ((m + 31) // 32),
+           "h2d_bytes_per_step": (17 if args.e2e_packed_meta else 18) * m, "d2h_bytes_per_step": 4 * ((m + 31) // 32),
            "n_emitted": len(batch), "device_ms_per_step": batch.stats["ms_total"],
            "h2d_only_gbs_this_rank": 26.0 * m / h2d_s / 1e9,
            "api": "PodWatcher.replay(ReplayLog in pinned memory) -> Batch (emit bitmap): pte_replay_pipelined underneath, "
-                  "chunks of %d events" % w.pipeline_chunk_events}
+                  "chunks of %d events%s" % (w.pipeline_chunk_events, "; type and phase travel as one packed byte (--e2e-packed-meta)" if args.e2e_packed_meta else "")}
     if m < ev:
         res["reduced"] = "host memory: %d ranks x 26 B x %d events do not fit in half of the free RAM; same shape, %d events per GPU" % (world, ev, m)
     log.free()

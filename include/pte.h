@@ -219,7 +219,9 @@ int pte_fetch_bitmap(pte_handle h, uint32_t* words, uint64_t cap_words, uint64_t
  * resourceVersion order (PTE_ERR_UNORDERED otherwise); ns_id may be NULL as in pte_ingest.  rv may be NULL too: the
  * caller then vouches that the log is in arrival order -- the only order the reference's loop knows, it never reads
  * metadata.resourceVersion -- and the position serves as order key (8 of the 26 bytes per event stay at home).
- * The log stays resident. */
+ * type may be NULL as well: phase[] then carries both, type << 6 | phase in one byte per event (PTE_PACK_META below), and is
+ * taken apart on the device -- 17 bytes per event over the wire.  The log stays resident. */
+#define PTE_PACK_META(type, phase) ((uint8_t)(((type) << 6) | ((phase) & 63)))
 int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* uid_lo, const uint64_t* rv,
                          const uint32_t* ns_id, const uint8_t* phase, const uint8_t* type, uint64_t n,
                          uint64_t chunk_events, int dedupe, uint32_t* bitmap_out, pte_stats* out);

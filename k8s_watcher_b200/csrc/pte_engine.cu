@@ -1196,7 +1196,7 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
                          uint32_t* bitmap_out, pte_stats* out) {
     if (!h) FAIL(h, PTE_ERR_INVALID, "handle is NULL");
     if (n > h->max_events) FAIL(h, PTE_ERR_CAPACITY, "log longer than the engine's max_events");
-    if (n && (!uid_hi || !uid_lo || !phase || !type || !bitmap_out)) FAIL(h, PTE_ERR_INVALID, "NULL column or bitmap");
+    if (n && (!uid_hi || !uid_lo || !phase || !bitmap_out)) FAIL(h, PTE_ERR_INVALID, "NULL column or bitmap");
     if (n && !ns_id && h->ns_filter_on) FAIL(h, PTE_ERR_INVALID, "ns_id may only be NULL while no namespace allow-list is set");
     CK(h, cudaSetDevice(h->device));
     if (!h->copy_stream) CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -1218,7 +1218,12 @@ int pte_replay_pipelined(pte_handle h, const uint64_t* uid_hi, const uint64_t* u
         if (rv) CK(h, cudaMemcpyAsync(h->rv + off, rv + off, len * 8, cudaMemcpyHostToDevice, cs));
         if (ns_id) CK(h, cudaMemcpyAsync(h->ns + off, ns_id + off, len * 4, cudaMemcpyHostToDevice, cs));
         CK(h, cudaMemcpyAsync(h->phase + off, phase + off, len, cudaMemcpyHostToDevice, cs));
-        CK(h, cudaMemcpyAsync(h->type + off, type + off, len, cudaMemcpyHostToDevice, cs));
+        if (type) CK(h, cudaMemcpyAsync(h->type + off, type + off, len, cudaMemcpyHostToDevice, cs));
+        else {
+            // one byte per event for both: type << 6 | phase, taken apart where it lands (still on the copy stream)
+            unpack_meta_kernel<<<(int)std::min<u64>((len / 16 + 255) / 256 + 1, (u64)h->num_sms * 8), 256, 0, cs>>>(h->phase + off, h->type + off, len);
+            CK(h, cudaGetLastError());
+        }
         CK(h, cudaEventCreateWithFlags(&landed[k], cudaEventDisableTiming));
         CK(h, cudaEventRecord(landed[k], cs));
     }

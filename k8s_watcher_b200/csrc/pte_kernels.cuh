@@ -520,6 +520,19 @@ diff_apply_kernel(const u32* __restrict__ list, const u32* __restrict__ cnt, u64
     }
 }
 
+// (type << 6 | phase) per event -> the two columns, 16 events per thread and step (the buffers are padded to a multiple of 16)
+__global__ void __launch_bounds__(256) unpack_meta_kernel(u8* __restrict__ phase, u8* __restrict__ type, u64 n) {
+    const u64 n16 = (n + 15) / 16;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (u64)gridDim.x * blockDim.x) {
+        uint4 m = reinterpret_cast<const uint4*>(phase)[i];
+        uint4 t;
+        t.x = (m.x >> 6) & 0x03030303u; t.y = (m.y >> 6) & 0x03030303u; t.z = (m.z >> 6) & 0x03030303u; t.w = (m.w >> 6) & 0x03030303u;
+        m.x &= 0x3F3F3F3Fu; m.y &= 0x3F3F3F3Fu; m.z &= 0x3F3F3F3Fu; m.w &= 0x3F3F3F3Fu;
+        reinterpret_cast<uint4*>(phase)[i] = m;
+        reinterpret_cast<uint4*>(type)[i] = t;
+    }
+}
+
 // ---- a dictionary that lives as long as the watch (pod_watcher.py:264-269 never ends) ------------------------
 // A stream's dictionary only ever gains uids: a DELETED pod keeps its slot with state 0.  When it fills up, the
 // slots whose state byte is not 0 (pods with a live last-known phase) are re-inserted into a fresh table and their

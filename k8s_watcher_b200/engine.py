@@ -33,6 +33,14 @@ def _ptr(a: Optional[np.ndarray], ctype):
     return None if a is None else a.ctypes.data_as(C.POINTER(ctype))
 
 
+def pack_meta(type_col: np.ndarray, phase_col: np.ndarray, out: Optional[np.ndarray] = None) -> np.ndarray:
+    """One byte per event for event type and phase: ``type << 6 | phase`` (PTE_PACK_META of include/pte.h)."""
+    out = np.empty(type_col.shape[0], np.uint8) if out is None else out
+    np.left_shift(type_col, 6, out=out, dtype=np.uint8, casting="unsafe")
+    np.bitwise_or(out, phase_col & np.uint8(63), out=out)
+    return out
+
+
 def generate_host(seed: int, n_events: int, n_pods: int, **kw) -> Dict[str, np.ndarray]:
     """The synthetic replay log of include/pte.h, generated on the host by libpte.so."""
     cols = {name: np.empty(n_events, dt) for name, dt in COLUMNS}
@@ -292,20 +300,27 @@ class PhaseTransitionEngine:
         return out[:words]
 
     def replay_pipelined(self, cols: Dict[str, np.ndarray], *, dedupe: bool = True, chunk_events: int = 0,
-                         with_namespaces: bool = True, with_rv: bool = True, bitmap_out: Optional[np.ndarray] = None):
+                         with_namespaces: bool = True, with_rv: bool = True, bitmap_out: Optional[np.ndarray] = None,
+                         meta: Optional[np.ndarray] = None):
         """ingest + run + fetch_bitmap as one pipelined call (pte_replay_pipelined): host -> device copies of later
         chunks overlap the replay of earlier ones.  Columns in pinned memory (PinnedBuffer) copy at full PCIe speed.
+        ``meta``: one byte per event, ``type << 6 | phase`` (pack_meta), sent instead of the phase and type columns.
         Returns (emit bitmap words, stats)."""
         n = int(cols["rv"].shape[0])
         c = {name: np.ascontiguousarray(cols[name], dtype=dt) for name, dt in COLUMNS}
+        if meta is not None:
+            meta = np.ascontiguousarray(meta, dtype=np.uint8)
+            if meta.shape[0] != n:
+                raise ValueError("meta has %d rows, the log %d" % (meta.shape[0], n))
         words = (n + 31) // 32
         out = bitmap_out if bitmap_out is not None else np.zeros(max(words, 1), np.uint32)
         st = PteStats()
         self._ck(self._L.pte_replay_pipelined(
             self._h, _ptr(c["uid_hi"], C.c_uint64), _ptr(c["uid_lo"], C.c_uint64),
             _ptr(c["rv"], C.c_uint64) if with_rv else None,      # with_rv=False: the caller vouches for arrival order
-            _ptr(c["ns_id"], C.c_uint32) if with_namespaces else None, _ptr(c["phase"], C.c_uint8),
-            _ptr(c["type"], C.c_uint8), n, int(chunk_events), int(bool(dedupe)), _ptr(out, C.c_uint32), C.byref(st)))
+            _ptr(c["ns_id"], C.c_uint32) if with_namespaces else None,
+            _ptr(c["phase"] if meta is None else meta, C.c_uint8), _ptr(c["type"], C.c_uint8) if meta is None else None,
+            n, int(chunk_events), int(bool(dedupe)), _ptr(out, C.c_uint32), C.byref(st)))
         self.last_stats = st.as_dict()
         return out[:words], self.last_stats
 

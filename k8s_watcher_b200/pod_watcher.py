@@ -364,7 +364,7 @@ class PodWatcher:
                 bitmap, stats = eng.replay_pipelined(log.columns, dedupe=dedupe, with_namespaces=bool(names),
                                                      with_rv=not log.arrival_ordered,
                                                      chunk_events=self.pipeline_chunk_events,
-                                                     bitmap_out=log.bitmap_buffer())
+                                                     bitmap_out=log.bitmap_buffer(), meta=log.meta)
                 batch = Batch(self, log, None, stats, dedupe, bitmap=bitmap)
                 self._remember(batch)
                 return batch

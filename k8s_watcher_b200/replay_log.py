@@ -30,6 +30,7 @@ class ReplayLog:
         # True: the rows are in the order the watcher received them and that IS the replay order (the reference's loop
         # knows no other; it never reads resourceVersion).  replay() then leaves the rv column on the host.
         self.arrival_ordered = False
+        self.meta = None             # pack_meta(): type << 6 | phase per event
         self.uids: Optional[codes.UidInterner] = None      # set by from_events: maps keys of non-UUID uids back
 
     def __len__(self):
@@ -46,6 +47,20 @@ class ReplayLog:
         log._pins = bufs
         log._bitmap_pin = PinnedBuffer((n_events + 31) // 32 + 1, np.uint32)
         return log
+
+    def pack_meta(self):
+        """Keep a packed (type, phase) byte per event beside the columns (pinned if the log is): replay() then sends that one
+        byte instead of two.  To be called again after phase or type columns change."""
+        from .engine import PinnedBuffer, pack_meta
+        n = len(self)
+        if getattr(self, "_pins", None):
+            pin = self._pins.get("meta")
+            if pin is None:
+                pin = self._pins["meta"] = PinnedBuffer(n, np.uint8)
+            self.meta = pack_meta(self.columns["type"], self.columns["phase"], out=pin.array)
+        else:
+            self.meta = pack_meta(self.columns["type"], self.columns["phase"])
+        return self.meta
 
     def bitmap_buffer(self):
         """Reusable destination of the emit bitmap (pinned if the log is), or None."""
