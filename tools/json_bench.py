@@ -37,6 +37,44 @@ with PhaseTransitionEngine(ne * rep + 16, 4000) as e:
         print("  pte_ingest_json wall, text as %s: %.1f ms = %.1f GB/s of text, %.1f M events/s" % (name, best * 1e3, gb / best, n / best / 1e6))
     pin.free()
 
+# pod objects of the size real clusters send (managedFields, several containers with env and mounts: 4-5 KB per event)
+import json as _json
+fat_meta = {"managedFields": [{"manager": "kube-controller-manager", "operation": "Update", "apiVersion": "v1", "time": "2025-01-01T00:00:00Z",
+                               "fieldsType": "FieldsV1", "fieldsV1": {"f:metadata": {"f:labels": {".": {}, "f:app": {}, "f:pod-template-hash": {}},
+                               "f:ownerReferences": {".": {}, "k:{\"uid\":\"00000000-dead-beef-0000-000000000000\"}": {}}},
+                               "f:spec": {"f:containers": {"k:{\"name\":\"main\"}": {".": {}, "f:image": {}, "f:env": {}, "f:resources": {}}}}}}] * 3}
+fat_spec = {"volumes": [{"name": "v%d" % k, "configMap": {"name": "cfg-%d" % k, "defaultMode": 420}} for k in range(4)],
+            "containers2": [{"name": "c%d" % k, "image": "registry.local/team/service-%d:1.2.%d" % (k, k),
+                             "env": [{"name": "ENV_%d" % j, "value": "value-%d" % j} for j in range(8)],
+                             "volumeMounts": [{"name": "v%d" % j, "mountPath": "/etc/cfg/%d" % j, "readOnly": True} for j in range(4)],
+                             "resources": {"limits": {"cpu": "500m", "memory": "512Mi"}, "requests": {"cpu": "100m", "memory": "128Mi"}}} for k in range(3)]}
+extra_meta = _json.dumps(fat_meta, separators=(",", ":"))[1:-1].encode()
+extra_spec = _json.dumps(fat_spec, separators=(",", ":"))[1:-1].encode()
+fat_lines = []
+for l in block.split(b"\n")[:40_000]:
+    if not l:
+        continue
+    for marker, extra in ((b'"metadata":{', extra_meta), (b'"metadata": {', extra_meta), (b'"spec":{', extra_spec), (b'"spec": {', extra_spec)):
+        i = l.find(marker)
+        if i >= 0 and b'"object"' in l[:i]:
+            l = l[:i + len(marker)] + extra + b"," + l[i + len(marker):]
+    fat_lines.append(l)
+fat = b"\n".join(fat_lines) + b"\n"
+fat_text = fat * max(1, int(1.0e9 // len(fat)))
+with PhaseTransitionEngine(len(fat_lines) * (len(fat_text) // len(fat)) + 16, 4000) as e:
+    small = PhaseTransitionEngine(len(fat_lines) + 16, 4000)
+    small.ingest_json(fat); fat_cols = small.read_log()
+    small.ingest_json(b"\n".join(block.split(b"\n")[:40_000])); thin_cols = small.read_log(); small.close()
+    assert all((fat_cols[k] == thin_cols[k]).all() for k in ("uid_hi", "uid_lo", "phase", "type", "ns_id")), "the padding changed what is read"
+    for _ in range(3):
+        n = e.ingest_json(fat_text)
+        t = e.json_timing()
+    gb = t["text_bytes"] / 1e9
+    print("watch JSON, pods of realistic size: %d lines, %.3f GB of text (%.0f B/line): line index %.3f ms, scanner kernel %.3f ms = %.0f GB/s of text "
+          "(%.3f of the measured %.1f GB/s HBM peak), %.1f M events/s on the device"
+          % (n, gb, t["text_bytes"] / n, t["ms_index"], t["ms_parse"], gb / (t["ms_parse"] * 1e-3), gb / (t["ms_parse"] * 1e-3) / peak,
+             peak, n / t["ms_parse"] / 1e3))
+
 # request bodies built on the device (pte_serialize_payloads): device time of the kernel that writes them
 import logging; logging.disable(logging.CRITICAL)
 from k8s_watcher_b200 import PodWatcher, ReplayLog
