@@ -135,7 +135,7 @@ PTE_JS_HD void set_field(Fields& f, u32 w, Span sp) {
 // some lane of the warp drags the other 31 through the key comparison and the value look-up.  An entry is four words:
 // where the key string starts, where the colon is, (key length | meaning of the container << 4 | distance from the colon
 // to the next opening quote << 8, all ones = none seen), and where that string closes (kNever = not seen).
-static constexpr u32 kQueueCap = 12, kNoDelta = 0xFFFFFFu;
+static constexpr u32 kQueueCap = 8, kNoDelta = 0xFFFFFFu;
 
 template <typename T, typename QS>
 PTE_JS_HD void flush_queue(const T& t, QS& q, u32& n_q, Fields& f) {

@@ -97,7 +97,7 @@ EDGE = [
     b'{"type":"ADDED","object":{"metadata":{"uid":                                             "far"}}}',
     b'{"type":"ADDED","object":{"metadata":{"labels":{"a":{"b":{"c":{"d":{"e":[[[[{"uid":"deep"}]]]]}}}}},"uid":"shallow"}}}',
     b'{"type":"ADDED","object":{"metadata":{"uid":"u"},"status":{"phase":"Running","conditions":[{"type":"Ready","phase":"no"}]}}}',
-    # more look-alike keys than the scanner's candidate queue holds (12): keys of the lengths it looks for, before, between and after the real ones
+    # more look-alike keys than the scanner's candidate queue holds (8): keys of the lengths it looks for, before, between and after the real ones
     ('{"type":"ADDED","object":{"metadata":{' + ",".join('"k%02d":"v%d"' % (k, k) for k in range(30)) + ',"uid":"u-mid",'
      + ",".join('"z%02d":%d' % (k, k) for k in range(30)) + ',"namespace":"ns-late","uid":"u-last"},"status":{'
      + ",".join('"p%04d":"x"' % k for k in range(20)) + ',"phase":"Running"}}}').encode(),
