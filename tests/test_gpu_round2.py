@@ -422,6 +422,13 @@ def test_device_json_decodes_escapes_in_every_field_it_reads():
         assert np.array_equal(got.columns[k], want.columns[k]), k
     assert got.namespaces == want.namespaces and np.array_equal(got.columns["ns_id"], want.columns["ns_id"])
     assert got.phases == want.phases and np.array_equal(got.columns["phase"], want.columns["phase"])
+    # ... and against what the text was made from, without any product code in between
+    for k in ("uid_hi", "uid_lo", "rv", "type"):
+        assert np.array_equal(got.columns[k], cols[k]), k
+    assert [got.namespaces[i] for i in got.columns["ns_id"].tolist()] == [ev["object"].metadata.namespace for ev in events]
+    for code, ev in zip(got.columns["phase"].tolist(), events):
+        st = ev["object"].status
+        assert (code == 6) if st is None else (code == 5) if st.phase is None else got.phases[code] == st.phase
 
 
 # ---- the raw watch stream as a live loop (SURVEY 8f rows 1 + 2): chunks of lines, state carried on the device ---------
