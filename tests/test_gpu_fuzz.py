@@ -110,3 +110,46 @@ def test_random_stream_batches_add_up_to_one_replay(shape, flt, cuts):
             tomb += stt["n_tombstones"]
     assert np.array_equal(np.concatenate(got), want.astype(np.int64))
     assert tomb == ost["n_tombstones"]
+
+
+# ---- the raw watch text as a stream, cut at random --------------------------------------------------------------
+json_shapes = st.fixed_dictionaries(dict(
+    seed=st.integers(0, 2**31), n=st.integers(1, 500), pods=st.integers(1, 40), dist=st.integers(0, 1),
+    p_del=st.sampled_from([0.0, 0.1, 0.6]), p_nostatus=st.sampled_from([0.0, 0.1]), p_null=st.sampled_from([0.0, 0.1])))
+
+
+@settings(max_examples=150, **COMMON)
+@given(shape=json_shapes, env=st.sampled_from(["development", "staging", "production"]), cut_seed=st.integers(0, 2**31),
+       dedupe=st.booleans())
+def test_random_watch_text_in_random_chunks(shape, env, cut_seed, dedupe):
+    """PodWatcher.watch_json on made-up streams: whatever the chunking, trailing newline or not, the notifications are the
+    reference's filters followed by the transition layer (dedupe) or the reference's own trace (no dedupe)."""
+    import os
+    import fake_kubernetes as fk
+    from k8s_watcher_b200 import PodWatcher
+    from oracle import podwatch_oracle as po
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cols = make_log(shape)
+    n = len(cols["rv"])
+    events = fk.events_from_columns(cols)
+    lines = [l for l in fk.watch_json_lines(events, seed=shape["seed"] % 1000).split(b"\n") if l]
+    where = {l: i for i, l in enumerate(lines)}
+    rnd = np.random.default_rng(cut_seed)
+    cuts = [0]
+    while cuts[-1] < n:
+        cuts.append(min(n, cuts[-1] + int(rnd.choice([1, 2, 3, 17, 64, 200]))))
+    chunks = [b"\n".join(lines[a:b]) + (b"\n" if rnd.random() < 0.5 else b"") for a, b in zip(cuts[:-1], cuts[1:])]
+    chunks.insert(int(rnd.integers(0, len(chunks) + 1)), b"")               # an empty read changes nothing
+    offs = iter(cuts[:-1])
+    w = PodWatcher(env, config_dir=os.path.join(root, "config"), max_pods=256, keep_batches=None)
+    w.logger.disabled = True
+    batches = w.watch_json(iter(chunks), lambda line: events[where[line]]["object"], dedupe=dedupe)
+    got = [int(i) + a for b, a in zip(batches, offs) for i in b.indices.tolist()]
+    reach = [i for i, e in enumerate(events) if po.reaches_post_site(env, w.config, e["type"], e["object"])]
+    if dedupe:
+        r = po.reference_trace(env, w.config, [(e["type"], e["object"]) for e in events], "T")
+        want = [reach[k] for k in po.transition_filter(r)]
+    else:
+        want = reach
+    assert got == want
+    w._engine.close()
