@@ -71,6 +71,8 @@ __device__ __forceinline__ void tiny_radix_pass(const u32* __restrict__ in, u32*
     for (u32 k = 0; k < kTinyPer; k++) {
         key[k] = in[warp * 128 + k * 32 + lane];
         const u32 d = (key[k] >> shift) & mask;
+        // (MATCH.ANY: eight per thread.  Peer masks through shared-memory atomics, as in the bulk radix pass, were measured
+        //  slower here: 38 against 32 us for the kernel -- more barriers, twice the counters to clear)
         const u32 peers = __match_any_sync(0xffffffffu, d);
         const u32 leader = __ffs(peers) - 1;
         u32 before = 0;
@@ -113,24 +115,42 @@ __global__ void __launch_bounds__(kTinyThreads) tiny_replay_kernel(TinyArgs a) {
     // ---- 1. columns in (and on into the engine's own arrays), predicates, interning, small ids ----
     const u64 pol = l2_policy_evict_last();
     u32 flags = 0, inserted = 0, del = 0, surv = 0;
+    {
+        // everything a thread needs of its (up to) four events is requested before anything is looked at: the loads of all
+        // columns, then the first probe of every kept event -- one memory latency each instead of four in a row
+        u64 hi[kTinyPer], lo[kTinyPer], rv[kTinyPer], before[kTinyPer];
+        u32 ns[kTinyPer], ph[kTinyPer], ty[kTinyPer], home[kTinyPer];
+        ulonglong2 pv[kTinyPer];
+        bool keep[kTinyPer];
 #pragma unroll
-    for (u32 k = 0; k < kTinyPer; k++) {
-        const u32 i = tid + k * kTinyThreads;
-        u32 key = kNoKey;
-        if (i < a.n) {
-            const u64 hi = a.src_hi[i], lo = a.src_lo[i], rv = a.src_rv[i];
-            const u32 ns = a.src_ns ? a.src_ns[i] : 0u, ph = a.src_phase[i], ty = a.src_type[i];
-            if (a.src_hi != a.uid_hi) { a.uid_hi[i] = hi; a.uid_lo[i] = lo; a.rv[i] = rv; a.ns[i] = ns; a.phase[i] = (u8)ph; a.type[i] = (u8)ty; }
-            const u64 before = i ? a.src_rv[i - 1] : a.prev_rv;
-            if (rv < before) flags |= kFlagUnordered;
-            bool keep = false;
-            if (ty > kTypeDeleted || ph > kPhMax) flags |= kFlagBadEvent;       // (as filter_flag_kernel: whatever the filters say)
-            else keep = passes_filters(a, ty, ph, ns);
-            if (keep && (hi | lo) == 0) { flags |= kFlagBadEvent; keep = false; }
-            if (keep) {
-                const u32 home = uid_home_slot(hi, lo, a.table_mask);
-                const ulonglong2 v = ld_slot(a.table + home, pol);
-                const u32 slot = intern_uid(a.table, a.table_mask, hi, lo, home, v, inserted, &s_flags, pol);
+        for (u32 k = 0; k < kTinyPer; k++) {
+            const u32 i = tid + k * kTinyThreads;
+            const bool in = i < a.n;
+            hi[k] = in ? a.src_hi[i] : 0; lo[k] = in ? a.src_lo[i] : 0; rv[k] = in ? a.src_rv[i] : 0;
+            before[k] = in ? (i ? a.src_rv[i - 1] : a.prev_rv) : 0;
+            ns[k] = in && a.src_ns ? a.src_ns[i] : 0u; ph[k] = in ? a.src_phase[i] : 0u; ty[k] = in ? a.src_type[i] : 0u;
+        }
+#pragma unroll
+        for (u32 k = 0; k < kTinyPer; k++) {
+            const u32 i = tid + k * kTinyThreads;
+            keep[k] = false;
+            pv[k] = make_ulonglong2(0, 0);
+            home[k] = 0;
+            if (i < a.n) {
+                if (a.src_hi != a.uid_hi) { a.uid_hi[i] = hi[k]; a.uid_lo[i] = lo[k]; a.rv[i] = rv[k]; a.ns[i] = ns[k]; a.phase[i] = (u8)ph[k]; a.type[i] = (u8)ty[k]; }
+                if (rv[k] < before[k]) flags |= kFlagUnordered;
+                if (ty[k] > kTypeDeleted || ph[k] > kPhMax) flags |= kFlagBadEvent;       // (as filter_flag_kernel: whatever the filters say)
+                else keep[k] = passes_filters(a, ty[k], ph[k], ns[k]);
+                if (keep[k] && (hi[k] | lo[k]) == 0) { flags |= kFlagBadEvent; keep[k] = false; }
+                if (keep[k]) { home[k] = uid_home_slot(hi[k], lo[k], a.table_mask); pv[k] = ld_slot(a.table + home[k], pol); }
+            }
+        }
+#pragma unroll
+        for (u32 k = 0; k < kTinyPer; k++) {
+            const u32 i = tid + k * kTinyThreads;
+            u32 key = kNoKey;
+            if (keep[k]) {
+                const u32 slot = intern_uid(a.table, a.table_mask, hi[k], lo[k], home[k], pv[k], inserted, &s_flags, pol);
                 // the slot's place in a set of at most 4 096 slots is its id for the sort (13 bits instead of 25)
                 u32 id = (slot * 0x9E3779B1u) >> 19;
                 for (;;) {
@@ -140,12 +160,12 @@ __global__ void __launch_bounds__(kTinyThreads) tiny_replay_kernel(TinyArgs a) {
                 }
                 key = (id << 12) | i;
                 s_slot[i] = slot;
-                s_meta[i] = (u8)(((ty & 3u) << 6) | (eff_phase(ph) & 63u));
-                del += ty == kTypeDeleted;
+                s_meta[i] = (u8)(((ty[k] & 3u) << 6) | (eff_phase(ph[k]) & 63u));
+                del += ty[k] == kTypeDeleted;
                 surv++;
             }
+            s_keyA[i] = key;
         }
-        s_keyA[i] = key;
     }
     inserted = __reduce_add_sync(0xffffffffu, inserted);
     del = __reduce_add_sync(0xffffffffu, del);
@@ -172,6 +192,13 @@ __global__ void __launch_bounds__(kTinyThreads) tiny_replay_kernel(TinyArgs a) {
     u8 tail_state[kTinyPer];
     u32 tails = 0;
     if (!failed) {
+        u32 st_[kTinyPer];
+#pragma unroll
+        for (u32 k = 0; k < kTinyPer; k++) {                               // the state bytes of the heads, all in flight together
+            const u32 i = tid + k * kTinyThreads;
+            const u32 cur = s_keyA[i], prev = i ? s_keyA[i - 1] : kNoKey;
+            st_[k] = (a.carry && cur != kNoKey && (prev >> 12) != (cur >> 12)) ? a.state[s_slot[cur & 0xFFFu]] : 0u;
+        }
 #pragma unroll
         for (u32 k = 0; k < kTinyPer; k++) {
             const u32 i = tid + k * kTinyThreads;
@@ -181,7 +208,7 @@ __global__ void __launch_bounds__(kTinyThreads) tiny_replay_kernel(TinyArgs a) {
             const u32 pos = cur & 0xFFFu, slot = s_slot[pos], m = s_meta[pos];
             bool emit;
             if ((prev >> 12) != (cur >> 12)) {                            // first record of this pod in the batch
-                const u32 st = a.carry ? a.state[slot] : 0u;
+                const u32 st = st_[k];
                 emit = (m & 0x80u) || st == 0 || st - 1 != (m & 0x3Fu);
             } else {
                 const u32 pm = s_meta[prev & 0xFFFu];
